@@ -1,0 +1,190 @@
+/* nbls.h — C ABI of libnbls, the B200 (sm_100a) narrow-band least-squares hot path.
+ *
+ * This is the drop-in boundary.  The reference
+ * (amiezzi/narrow_band_least_squares, pure Python) has no FFI of its own; each entry
+ * point below replaces one Python-level call on its hot path and is what a ctypes stub
+ * inside the reference would bind.  Citations are relative to the
+ * reference tree.
+ *
+ *   nbls_filter      <- helpers.py:108-141 filter_data (obspy zero-phase Butterworth
+ *                       band-pass / causal cheby1 + 1 % Hann taper), all bands at once
+ *   nbls_xcorr       <- lts_array/lts_array/classes/lts_classes.py:852-880
+ *                       LsBeam.correlate (np.correlate 'full' + argmax), all bands/windows
+ *   nbls_solve       <- lts_classes.py:873-878 (mdccm, MAD), :891-936 OLSEstimator.solve,
+ *                       :58-150 fast_LTS, :643-764 post_process (no uncertainty ellipse)
+ *   nbls_run_device  <- narrow_band_least_squares.py:67-124 band loop body, device buffers
+ *   nbls_run_host    <- the same with HOST buffers (H2D + path + D2H)
+ *
+ * Conventions: plain pointers and sizes, no C++ or torch types.  `*_dev` pointers are
+ * device memory owned by the caller; every other pointer is host memory and is read
+ * before the call returns.  All calls are ordered on the context's stream and
+ * return after enqueueing unless stated; nbls_synchronize() waits.  Return value 0 = OK,
+ * otherwise an NBLS_ERR_* code and nbls_last_error() describes it.  One context per GPU;
+ * a context is not thread-safe.  There is no CPU fallback: without a CUDA device
+ * nbls_create fails.
+ */
+#ifndef NBLS_H_
+#define NBLS_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NBLS_VERSION 100
+
+#define NBLS_OK 0
+#define NBLS_ERR_ARG 1
+#define NBLS_ERR_CUDA 2
+#define NBLS_ERR_NOMEM 3
+#define NBLS_ERR_UNSUPPORTED 4
+
+#define NBLS_MAX_SECTIONS 8
+#define NBLS_MAX_BANDS 256
+
+#define NBLS_XCORR_AUTO 0
+#define NBLS_XCORR_DIRECT 1 /* time-domain FP64 contraction over the circularly padded window */
+#define NBLS_XCORR_FFT 2    /* shared-memory FP64 FFT + exact re-evaluation of near-tied lags */
+
+typedef struct nbls_ctx nbls_ctx;
+
+/* ---- K1: per-band IIR band-pass (cascaded biquads) + taper ------------------------- */
+typedef struct nbls_filter_desc {
+    int32_t nbands;        /* B */
+    int32_t nsections;     /* S second-order sections per band (<= NBLS_MAX_SECTIONS) */
+    const double* sos;     /* [B][S][6] scipy layout b0 b1 b2 a0 a1 a2, a0 == 1 */
+    int32_t zerophase;     /* 1: forward pass then pass over the reversed signal, zero state
+                              twice (obspy zerophase=True, helpers.py:127); 0: one causal
+                              pass (cheby1 branch, helpers.py:131-137) */
+    int32_t exact_scan;    /* 1: chunk end-states from whole chunks (exact linear scan);
+                              0: from the last K_b samples only, K_b = decay length of band b
+                              to 2^-80 (contribution below FP64 rounding) */
+    int32_t chunk_len;     /* scan chunk length in samples (multiple of 16); 0 = auto */
+    int32_t reserved0;
+    int64_t taper_len;     /* wlen of obspy Trace.taper(0.01) (helpers.py:139); 0 = none */
+    const double* taper_up;   /* [taper_len] multipliers of global samples 0 .. wlen-1 */
+    const double* taper_down; /* [taper_len] multipliers of global samples G-wlen .. G-1 */
+    int64_t global_t0;     /* global index of local sample 0 (time-sharded segments) */
+    int64_t global_npts;   /* G: length of the whole record the taper refers to */
+} nbls_filter_desc;
+
+/* x_dev: [nchan] rows of npts doubles, row stride ldx.  y_dev: [B][nchan] rows, row stride
+ * ldy, band stride ystride_band (doubles).  Rows must be 16-byte aligned: pointers aligned
+ * to 16 bytes and strides even.  y may not alias x. */
+int nbls_filter(nbls_ctx* ctx, const nbls_filter_desc* desc, const double* x_dev, int32_t nchan,
+                int64_t npts, int64_t ldx, double* y_dev, int64_t ldy, int64_t ystride_band);
+
+/* ---- K2: windowed pairwise cross-correlation --------------------------------------- */
+typedef struct nbls_window_desc {
+    int32_t nbands;
+    int32_t max_lag;          /* < 0: all 2N-1 lags (reference behaviour); else |lag| <= max_lag */
+    int32_t method;           /* NBLS_XCORR_* */
+    int32_t reserved0;
+    const int32_t* win_len;   /* [B] N_b  = int(window_length*fs)       lts_data_class.py:58 */
+    const int32_t* win_hop;   /* [B] H_b  = int(round((1-ov)*N_b))      lts_data_class.py:60 */
+    const int64_t* win_first; /* [B] local sample index of window 0 of the band */
+    const int32_t* win_count; /* [B] W_b windows in the band            lts_data_class.py:63 */
+} nbls_window_desc;
+
+/* Outputs are window-major: row e = (sum of W_b' for b' < b) + w holds the P = C(C-1)/2
+ * pairs in the reference's idx_pair order (i<j, row-major; lts_classes.py:840).
+ * lag = argmax_m cij[m] - (N-1)  (first maximum wins; zero-energy pair -> -(N-1));
+ * tau = -lag/fs (lts_classes.py:875-876).  cmax = max_m cij[m] (normalised), NaN for a
+ * zero-energy pair.  cmax_dev may be NULL. */
+int nbls_xcorr(nbls_ctx* ctx, const nbls_window_desc* win, const double* y_dev, int32_t nchan,
+               int64_t ldy, int64_t ystride_band, int32_t* lag_dev, double* cmax_dev);
+
+/* ---- K3: per-window statistics and slowness solve ---------------------------------- */
+typedef struct nbls_solve_desc {
+    int32_t nchan;            /* C */
+    int32_t npairs;           /* P */
+    double fs;
+    const double* xij;        /* [P][2] co-array, km          lts_classes.py:842-843 */
+    const double* xij_mad;    /* [2]                          lts_classes.py:846-850 */
+    const double* ols_gain;   /* [2][P] pseudo-inverse of xij_standardized (OLS, :889,:917) */
+    double alpha;             /* 1.0 = OLS; [0.5,1) = FAST-LTS */
+    /* FAST-LTS only (alpha < 1): */
+    int32_t h;                /* subset size                  lts_classes.py:1013 */
+    int32_t n_starts;         /* 500                          lts_classes.py:991  */
+    int32_t n_keep;           /* 10                           lts_classes.py:993  */
+    int32_t csteps1;          /* 4                            lts_classes.py:995  */
+    int32_t csteps2;          /* 100                          lts_classes.py:997  */
+    int32_t reserved0;
+    const int32_t* subsets;   /* [n_starts + n_keep][2] the LCG stream of random_set(P,2,seed)
+                                 restarted at seed 0 (lts_classes.py:16-36,76) */
+    double raw_factor;        /* raw_corfactor*raw_consfactor lts_classes.py:646-648 */
+    double rew_factor1;       /* rew_corfactor                lts_classes.py:650 */
+    const double* rew_cons;   /* [P+1] rew_consfactor by number of unit weights (:326-344) */
+} nbls_solve_desc;
+
+/* Device output block of one run, all window-major over E = sum_b W_b rows.
+ * NULL members are not written / not copied. */
+typedef struct nbls_outputs {
+    double* mdccm;      /* [E] nanmedian of cmax over pairs          lts_classes.py:873 */
+    double* mad;        /* [E] 1.4826*median|tau|                    lts_classes.py:877-878 */
+    double* vel;        /* [E] trace velocity km/s, NaN if skipped   lts_classes.py:928,:706 */
+    double* baz;        /* [E] back-azimuth deg                      lts_classes.py:931,:713 */
+    double* sigma_tau;  /* [E]                                       lts_classes.py:934-936,:723-730 */
+    double* slowness;   /* [E][2] final slowness vector (s/km) */
+    int32_t* lag;       /* [E][P] */
+    double* cmax;       /* [E][P] */
+    uint8_t* weights;   /* [E][P] final LTS weights (element_weights, :701,:762); alpha<1 only */
+} nbls_outputs;
+
+int nbls_solve(nbls_ctx* ctx, const nbls_solve_desc* sol, int64_t nwin, const int32_t* lag_dev,
+               const double* cmax_dev, const nbls_outputs* out_dev);
+
+/* ---- whole path --------------------------------------------------------------------- */
+typedef struct nbls_job {
+    nbls_filter_desc filter;
+    nbls_window_desc window;
+    nbls_solve_desc solve;
+} nbls_job;
+
+/* Filter -> xcorr -> solve for every band and window of the job, data resident on the
+ * device.  x_dev as in nbls_filter.  `out_dev` members are device pointers (lag must be
+ * non-NULL; cmax may be NULL and is then kept in workspace). */
+int nbls_run_device(nbls_ctx* ctx, const nbls_job* job, const double* x_dev, int32_t nchan,
+                    int64_t npts, int64_t ldx, const nbls_outputs* out_dev);
+
+/* The same with host buffers: copies x (nchan rows, stride ldx_host) to the device, runs
+ * the path, copies every non-NULL member of `out_host` back, and synchronises.  Use
+ * nbls_malloc_host / nbls_host_register for pinned buffers. */
+int nbls_run_host(nbls_ctx* ctx, const nbls_job* job, const double* x_host, int32_t nchan,
+                  int64_t npts, int64_t ldx_host, const nbls_outputs* out_host);
+
+/* ---- context, memory, diagnostics --------------------------------------------------- */
+int nbls_version(void);
+const char* nbls_last_error(void);
+int nbls_device_count(int32_t* count);
+int nbls_create(nbls_ctx** ctx, int32_t device);
+int nbls_destroy(nbls_ctx* ctx);
+int nbls_synchronize(nbls_ctx* ctx);
+/* Upper bound of device workspace the context may hold (bytes); 0 = 80 % of free memory. */
+int nbls_set_workspace_limit(nbls_ctx* ctx, size_t bytes);
+
+int nbls_malloc_device(nbls_ctx* ctx, void** ptr, size_t bytes);
+int nbls_free_device(nbls_ctx* ctx, void* ptr);
+int nbls_malloc_host(void** ptr, size_t bytes); /* pinned */
+int nbls_free_host(void* ptr);
+int nbls_host_register(void* ptr, size_t bytes);
+int nbls_host_unregister(void* ptr);
+int nbls_memcpy_h2d(nbls_ctx* ctx, void* dst_dev, const void* src_host, size_t bytes);
+int nbls_memcpy_d2h(nbls_ctx* ctx, void* dst_host, const void* src_dev, size_t bytes);
+
+/* Device time of the stages of the last nbls_run_* call, milliseconds, measured with CUDA
+ * events on the context's stream: [0] H2D, [1] filter, [2] xcorr, [3] solve, [4] D2H,
+ * [5] total.  Synchronises.  Returns the number of values written (<= n). */
+int nbls_last_timings(nbls_ctx* ctx, float* ms, int32_t n);
+/* Kernel launches issued by this context since creation (for bench.py's gpu_launches). */
+int64_t nbls_launch_count(nbls_ctx* ctx);
+/* Register-resident DFMA throughput microbenchmark: returns FP64 TFLOP/s (2 flop per FMA)
+ * measured over `iters` dependent-chain iterations on every SM. */
+int nbls_measure_fp64_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBLS_H_ */

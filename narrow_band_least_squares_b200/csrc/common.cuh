@@ -1,0 +1,80 @@
+// common.cuh — context, error plumbing and small device helpers shared by the libnbls kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+#include "nbls.h"
+
+namespace nbls {
+
+void set_error(const char* fmt, ...);
+
+#define NBLS_CUDA(expr)                                                                      \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            ::nbls::set_error("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr,             \
+                              cudaGetErrorString(e__));                                      \
+            return NBLS_ERR_CUDA;                                                            \
+        }                                                                                    \
+    } while (0)
+
+#define NBLS_CHECK(expr)            \
+    do {                            \
+        int rc__ = (expr);          \
+        if (rc__ != NBLS_OK) return rc__; \
+    } while (0)
+
+#define NBLS_REQUIRE(cond, ...)             \
+    do {                                    \
+        if (!(cond)) {                      \
+            ::nbls::set_error(__VA_ARGS__); \
+            return NBLS_ERR_ARG;            \
+        }                                   \
+    } while (0)
+
+// A grow-only device buffer cached in the context (bench steps pay no cudaMalloc).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+enum { EV_START = 0, EV_H2D, EV_FILTER, EV_XCORR, EV_SOLVE, EV_D2H, EV_COUNT };
+
+}  // namespace nbls
+
+struct nbls_ctx {
+    int device = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    size_t ws_limit = 0;
+    int64_t launches = 0;
+    // cached buffers
+    nbls::DevBuf coef, state, carry, taper, filt, geom, lts_tab, xin, res, lagbuf, cmaxbuf, wbuf, scratch;
+    cudaEvent_t ev[nbls::EV_COUNT] = {};
+    bool ev_valid = false;
+    float stage_ms[6] = {};
+};
+
+namespace nbls {
+
+int ensure(nbls_ctx* ctx, DevBuf& b, size_t bytes);
+
+// stage implementations (each in its own .cu)
+int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C, int64_t T,
+                int64_t ldx, double* y, int64_t ldy, int64_t ystride_band);
+int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C, int64_t ldy,
+               int64_t ystride_band, int32_t* lag, double* cmax);
+int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_t* lag,
+               const double* cmax, const nbls_outputs* out);
+int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
+
+static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+}  // namespace nbls

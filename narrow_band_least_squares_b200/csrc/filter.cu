@@ -1,0 +1,404 @@
+// filter.cu — K1: per-band IIR band-pass as cascaded biquads over every channel x band, with a
+// time-chunked scan of the linear-recurrence state, and the Hann taper fused into the last store.
+//
+// Replaces helpers.py:108-141 filter_data of the reference (obspy Stream.filter('bandpass',
+// zerophase=True) = scipy sosfilt forward, then sosfilt over the reversed output, zero state
+// both times, no padding; then Trace.taper(0.01)).  The recurrence is scipy's direct-form-II
+// transposed section loop with the SAME unfused multiply/add order, so a chunk
+// that starts from the true state reproduces scipy bit for bit.
+//
+// Parallel structure (per direction):
+//   phase 1  every chunk of L samples runs from zero state over its last K_b samples (all of
+//            them in exact mode) and stores its end state                    -> reads only
+//   phase 2  one thread per (band, channel) carries states across chunks:
+//            s_in[k+1] = A_b^L s_in[k] + e[k]          (A_b^L from the host, FP64)
+//   phase 3  every chunk reruns from its true state and writes its output  -> read + write
+// A warp owns 32 consecutive chunks of one (band, channel); lanes walk their chunks in
+// lockstep, so each step moves a [32 chunks x 16 samples] tile: cp.async (16 B per lane,
+// eight lanes per 128-B line) into a padded shared-memory tile, lane r computes row r, and the
+// results leave through the same tile as full 128-B lines.
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <complex>
+#include <vector>
+
+#include "common.cuh"
+
+namespace nbls {
+
+constexpr int FT_TILE = 16;    // samples per chunk per step (one 128-B line)
+constexpr int FT_ROW = 18;     // padded row stride in doubles: 144 B keeps 16-B alignment and
+                               // makes lane r's LDS.128 hit banks 4r..4r+3 (conflict-free)
+constexpr int FT_STAGES = 3;   // cp.async ring depth
+constexpr int FT_WARPS = 4;    // bands per block
+constexpr int FT_TILE_DOUBLES = 32 * FT_ROW;
+
+struct FilterArgs {
+    const double* in;
+    int64_t in_row, in_band;   // in_band == 0: every band reads the same rows (the raw record)
+    double* out;               // nullptr: phase 1 (states only)
+    int64_t out_row, out_band;
+    const double* coef;        // [B][S][5] b0 b1 b2 a1 a2
+    const int* proc_tiles;     // [B] tiles per chunk to run in phase 1 (from the chunk's end)
+    const double* state_in;    // [B][C][nchunks][2S] or nullptr (zero)
+    double* state_out;         // same layout or nullptr
+    int B, C;
+    int64_t T;
+    int L, nchunks;
+    const double* taper_up;
+    const double* taper_down;
+    int64_t taper_len, g0, G;
+};
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gsrc), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+template <int S, bool REV>
+__global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs a) {
+    extern __shared__ __align__(16) double smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int band = blockIdx.x * FT_WARPS + warp;
+    if (band >= a.B) return;   // warps are independent: only warp-level synchronisation below
+    const int chan = blockIdx.z;
+    const int64_t chunk0 = (int64_t)blockIdx.y * 32;
+    double* ring = smem + warp * (FT_STAGES * FT_TILE_DOUBLES);
+    const int ntiles = a.L / FT_TILE;
+    int first = 0;
+    if (a.proc_tiles) first = ntiles - min(ntiles, a.proc_tiles[band]);
+
+    const double* in = a.in + (int64_t)band * a.in_band + (int64_t)chan * a.in_row;
+    double* out = a.out ? a.out + (int64_t)band * a.out_band + (int64_t)chan * a.out_row : nullptr;
+
+    double b0[S], b1[S], b2[S], a1[S], a2[S], z0[S], z1[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const double* c = a.coef + ((int64_t)band * S + s) * 5;
+        b0[s] = c[0]; b1[s] = c[1]; b2[s] = c[2]; a1[s] = c[3]; a2[s] = c[4];
+        z0[s] = 0.0; z1[s] = 0.0;
+    }
+    const int64_t mychunk = chunk0 + lane;
+    const bool valid = mychunk < a.nchunks;
+    const int64_t sidx = (((int64_t)band * a.C + chan) * a.nchunks + mychunk) * (2 * S);
+    if (a.state_in && valid) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) { z0[s] = a.state_in[sidx + 2 * s]; z1[s] = a.state_in[sidx + 2 * s + 1]; }
+    }
+
+    // the copy this lane performs for each of its 8 slots of a tile: row = slot*4 + lane/8
+    const int seg = lane & 7;
+    auto tile_off = [&](int i) -> int { return FT_TILE * (REV ? (ntiles - 1 - i) : i); };
+    auto issue = [&](int i, int stage) {
+        double* dst0 = ring + stage * FT_TILE_DOUBLES;
+        const int off = tile_off(i) + seg * 2;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int row = q * 4 + (lane >> 3);
+            const int64_t k = chunk0 + row;
+            const int64_t t = k * a.L + off;
+            int bytes = 0;
+            if (k < a.nchunks) {
+                const int64_t left = a.T - t;
+                bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
+            }
+            cp_async16(dst0 + row * FT_ROW + seg * 2, bytes ? (const void*)(in + t) : (const void*)in, bytes);
+        }
+    };
+
+#pragma unroll
+    for (int s = 0; s < FT_STAGES - 1; ++s) {
+        if (first + s < ntiles) issue(first + s, s);
+        cp_async_commit();
+    }
+    int stage = 0;
+    for (int i = first; i < ntiles; ++i) {
+        {
+            const int nxt = i + FT_STAGES - 1;
+            int nstage = stage + FT_STAGES - 1;
+            if (nstage >= FT_STAGES) nstage -= FT_STAGES;
+            if (nxt < ntiles) issue(nxt, nstage);
+            cp_async_commit();
+        }
+        cp_async_wait<FT_STAGES - 1>();
+        __syncwarp();
+        double* tile = ring + stage * FT_TILE_DOUBLES;
+        double2* row = reinterpret_cast<double2*>(tile + lane * FT_ROW);
+        double v[FT_TILE];
+#pragma unroll
+        for (int q = 0; q < FT_TILE / 2; ++q) {
+            double2 d = row[q];
+            v[2 * q] = d.x; v[2 * q + 1] = d.y;
+        }
+#pragma unroll
+        for (int jj = 0; jj < FT_TILE; ++jj) {
+            const int j = REV ? (FT_TILE - 1 - jj) : jj;
+            double x = v[j];
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                // scipy _sosfilt order, unfused
+                const double y = __dadd_rn(__dmul_rn(b0[s], x), z0[s]);
+                z0[s] = __dadd_rn(__dsub_rn(__dmul_rn(b1[s], x), __dmul_rn(a1[s], y)), z1[s]);
+                z1[s] = __dsub_rn(__dmul_rn(b2[s], x), __dmul_rn(a2[s], y));
+                x = y;
+            }
+            v[j] = x;
+        }
+        if (out) {
+#pragma unroll
+            for (int q = 0; q < FT_TILE / 2; ++q) row[q] = make_double2(v[2 * q], v[2 * q + 1]);
+            __syncwarp();
+            const int off = tile_off(i) + seg * 2;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int r = q * 4 + (lane >> 3);
+                const int64_t k = chunk0 + r;
+                const int64_t t = k * a.L + off;
+                if (k < a.nchunks && t < a.T) {
+                    double2 d = *reinterpret_cast<const double2*>(tile + r * FT_ROW + seg * 2);
+                    if (a.taper_len > 0) {
+                        const int64_t g = a.g0 + t;
+                        const int64_t dn = a.G - a.taper_len;
+                        if (g < a.taper_len) d.x = __dmul_rn(d.x, a.taper_up[g]);
+                        if (g + 1 < a.taper_len) d.y = __dmul_rn(d.y, a.taper_up[g + 1]);
+                        if (g >= dn && g < a.G) d.x = __dmul_rn(d.x, a.taper_down[g - dn]);
+                        if (g + 1 >= dn && g + 1 < a.G) d.y = __dmul_rn(d.y, a.taper_down[g + 1 - dn]);
+                    }
+                    if (t + 1 < a.T) *reinterpret_cast<double2*>(out + t) = d;
+                    else out[t] = d.x;
+                }
+            }
+        }
+        __syncwarp();
+        if (++stage == FT_STAGES) stage = 0;
+    }
+    cp_async_wait<0>();
+    if (a.state_out && valid) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) { a.state_out[sidx + 2 * s] = z0[s]; a.state_out[sidx + 2 * s + 1] = z1[s]; }
+    }
+}
+
+// phase 2: state[k] (chunk end states from zero) -> state[k] (true chunk start states)
+__global__ void carry_kernel(double* state, const double* ML, int B, int C, int nchunks, int S2, int reverse) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= B * C) return;
+    const int band = id / C;
+    const double* M = ML + (int64_t)band * S2 * S2;
+    double* st = state + (int64_t)id * nchunks * S2;
+    double s[2 * NBLS_MAX_SECTIONS], e[2 * NBLS_MAX_SECTIONS], t[2 * NBLS_MAX_SECTIONS];
+    for (int i = 0; i < S2; ++i) s[i] = 0.0;
+    for (int step = 0; step < nchunks; ++step) {
+        const int k = reverse ? nchunks - 1 - step : step;
+        double* p = st + (int64_t)k * S2;
+        for (int i = 0; i < S2; ++i) { e[i] = p[i]; p[i] = s[i]; }
+        for (int i = 0; i < S2; ++i) {
+            double acc = e[i];
+            for (int j = 0; j < S2; ++j) acc = fma(M[i * S2 + j], s[j], acc);
+            t[i] = acc;
+        }
+        for (int i = 0; i < S2; ++i) s[i] = t[i];
+    }
+}
+
+typedef void (*chunk_fn)(FilterArgs);
+template <int S>
+static chunk_fn pick_dir(bool rev) { return rev ? biquad_chunk_kernel<S, true> : biquad_chunk_kernel<S, false>; }
+static chunk_fn pick(int S, bool rev) {
+    switch (S) {
+        case 1: return pick_dir<1>(rev);
+        case 2: return pick_dir<2>(rev);
+        case 3: return pick_dir<3>(rev);
+        case 4: return pick_dir<4>(rev);
+        case 5: return pick_dir<5>(rev);
+        case 6: return pick_dir<6>(rev);
+        case 7: return pick_dir<7>(rev);
+        case 8: return pick_dir<8>(rev);
+    }
+    return nullptr;
+}
+
+// one zero-input step of the DF2T cascade as a (2S x 2S) matrix, then its L-th power
+static void transition_power(const double* sos, int S, int64_t L, std::vector<double>& out) {
+    const int n = 2 * S;
+    std::vector<long double> M(n * n, 0.0L), R(n * n, 0.0L), Tm(n * n);
+    for (int col = 0; col < n; ++col) {
+        std::vector<long double> z(n, 0.0L);
+        z[col] = 1.0L;
+        long double x = 0.0L;
+        for (int s = 0; s < S; ++s) {
+            const long double b0 = sos[s * 6 + 0], b1 = sos[s * 6 + 1], b2 = sos[s * 6 + 2];
+            const long double a1 = sos[s * 6 + 4], a2 = sos[s * 6 + 5];
+            const long double y = b0 * x + z[2 * s];
+            const long double n0 = b1 * x - a1 * y + z[2 * s + 1];
+            const long double n1 = b2 * x - a2 * y;
+            z[2 * s] = n0; z[2 * s + 1] = n1;
+            x = y;
+        }
+        for (int r = 0; r < n; ++r) M[r * n + col] = z[r];
+    }
+    for (int i = 0; i < n; ++i) R[i * n + i] = 1.0L;
+    auto mul = [&](std::vector<long double>& A, const std::vector<long double>& Bm) {
+        for (int i = 0; i < n; ++i)
+            for (int j = 0; j < n; ++j) {
+                long double acc = 0.0L;
+                for (int k = 0; k < n; ++k) acc += A[i * n + k] * Bm[k * n + j];
+                Tm[i * n + j] = acc;
+            }
+        A = Tm;
+    };
+    int64_t e = L;
+    while (e > 0) {
+        if (e & 1) mul(R, M);
+        e >>= 1;
+        if (e) { std::vector<long double> M2 = M; mul(M, M2); }
+    }
+    out.resize(n * n);
+    for (int i = 0; i < n * n; ++i) out[i] = (double)R[i];
+}
+
+static double max_pole_radius(const double* sos, int S) {
+    double r = 0.0;
+    for (int s = 0; s < S; ++s) {
+        const double a1 = sos[s * 6 + 4], a2 = sos[s * 6 + 5];
+        const double disc = a1 * a1 - 4.0 * a2;
+        double m;
+        if (disc < 0) m = sqrt(fabs(a2));
+        else m = std::max(fabs((-a1 + sqrt(disc)) * 0.5), fabs((-a1 - sqrt(disc)) * 0.5));
+        r = std::max(r, m);
+    }
+    return r;
+}
+
+int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C, int64_t T, int64_t ldx,
+                double* y, int64_t ldy, int64_t ystride_band) {
+    NBLS_REQUIRE(d && x && y, "nbls_filter: null argument");
+    const int B = d->nbands, S = d->nsections;
+    NBLS_REQUIRE(B >= 1 && B <= NBLS_MAX_BANDS, "nbls_filter: nbands %d out of range", B);
+    NBLS_REQUIRE(S >= 1 && S <= NBLS_MAX_SECTIONS, "nbls_filter: nsections %d out of range [1,%d]", S,
+                 NBLS_MAX_SECTIONS);
+    NBLS_REQUIRE(C >= 1 && C <= 65535 && T >= 1, "nbls_filter: bad shape C=%d T=%lld", C, (long long)T);
+    NBLS_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0 && (ldx & 1) == 0 && (ldy & 1) == 0 &&
+                     (ystride_band & 1) == 0,
+                 "nbls_filter: rows must be 16-byte aligned (even strides, aligned base)");
+    NBLS_REQUIRE(ldx >= T && ldy >= T, "nbls_filter: row stride shorter than npts");
+    for (int i = 0; i < B * S; ++i)
+        NBLS_REQUIRE(d->sos[i * 6 + 3] == 1.0, "nbls_filter: sos[:,3] must be 1 (scipy sosfilt contract)");
+    NBLS_REQUIRE(d->taper_len >= 0 && (d->taper_len == 0 || (d->taper_up && d->taper_down)),
+                 "nbls_filter: taper arrays missing");
+
+    // chunking
+    int64_t L = d->chunk_len;
+    if (L <= 0) {
+        L = round_up((int64_t)((double)T * B * C / 131072.0), FT_TILE);
+        L = std::max<int64_t>(256, std::min<int64_t>(65536, L));
+    }
+    NBLS_REQUIRE(L % FT_TILE == 0 && L >= FT_TILE, "nbls_filter: chunk_len must be a positive multiple of %d", FT_TILE);
+    L = std::min<int64_t>(L, round_up(T, FT_TILE));
+    const int64_t nchunks64 = (T + L - 1) / L;
+    NBLS_REQUIRE(nchunks64 <= (1 << 26), "nbls_filter: too many chunks");
+    const int nchunks = (int)nchunks64;
+    const int ntiles = (int)(L / FT_TILE);
+    const int S2 = 2 * S;
+
+    // host-side tables: coefficients, A^L, phase-1 lengths
+    const size_t n_coef = (size_t)B * S * 5, n_ml = (size_t)B * S2 * S2;
+    std::vector<double> hbuf(n_coef + n_ml);
+    std::vector<int> hproc(B);
+    for (int b = 0; b < B; ++b) {
+        const double* sb = d->sos + (size_t)b * S * 6;
+        for (int s = 0; s < S; ++s) {
+            double* c = &hbuf[((size_t)b * S + s) * 5];
+            c[0] = sb[s * 6 + 0]; c[1] = sb[s * 6 + 1]; c[2] = sb[s * 6 + 2];
+            c[3] = sb[s * 6 + 4]; c[4] = sb[s * 6 + 5];
+        }
+        std::vector<double> ml;
+        transition_power(sb, S, L, ml);
+        memcpy(&hbuf[n_coef + (size_t)b * S2 * S2], ml.data(), sizeof(double) * S2 * S2);
+        int pt = ntiles;
+        if (!d->exact_scan) {
+            const double r = max_pole_radius(sb, S);
+            if (r > 0.0 && r < 1.0) {
+                const double K = ceil(80.0 * M_LN2 / -log(r));
+                if (K < (double)L) pt = (int)std::min<double>(ntiles, ceil(K / FT_TILE));
+            } else if (r == 0.0) {
+                pt = std::min(ntiles, 2 * S / FT_TILE + 1);   // FIR: state forgets after 2 samples/section
+            }
+        }
+        hproc[b] = pt;
+    }
+    const size_t coef_bytes = hbuf.size() * sizeof(double) + round_up(B * sizeof(int), 16);
+    NBLS_CHECK(ensure(ctx, ctx->coef, coef_bytes));
+    double* dcoef = (double*)ctx->coef.p;
+    double* dml = dcoef + n_coef;
+    int* dproc = (int*)(dml + n_ml);
+    NBLS_CUDA(cudaMemcpyAsync(dcoef, hbuf.data(), hbuf.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    NBLS_CUDA(cudaMemcpyAsync(dproc, hproc.data(), B * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    // pageable sources: the copies above are staged before returning, but be explicit
+    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+
+    const double *dup = nullptr, *ddown = nullptr;
+    if (d->taper_len > 0) {
+        NBLS_CHECK(ensure(ctx, ctx->taper, 2 * d->taper_len * sizeof(double)));
+        double* tp = (double*)ctx->taper.p;
+        NBLS_CUDA(cudaMemcpyAsync(tp, d->taper_up, d->taper_len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        NBLS_CUDA(cudaMemcpyAsync(tp + d->taper_len, d->taper_down, d->taper_len * sizeof(double),
+                                  cudaMemcpyHostToDevice, ctx->stream));
+        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+        dup = tp;
+        ddown = tp + d->taper_len;
+    }
+    double* dstate = nullptr;
+    if (nchunks > 1) {
+        NBLS_CHECK(ensure(ctx, ctx->state, (size_t)B * C * nchunks * S2 * sizeof(double)));
+        dstate = (double*)ctx->state.p;
+    }
+
+    const size_t smem = (size_t)FT_WARPS * FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
+    const dim3 grid((B + FT_WARPS - 1) / FT_WARPS, (nchunks + 31) / 32, C);
+    NBLS_REQUIRE(grid.y <= 65535, "nbls_filter: chunk grid too large (raise chunk_len)");
+    for (int rev = 0; rev < 2; ++rev) {
+        chunk_fn fn = pick(S, rev != 0);
+        NBLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+
+    auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
+        chunk_fn fn = pick(S, rev);
+        FilterArgs a;
+        memset(&a, 0, sizeof(a));
+        a.in = in; a.in_row = in_row; a.in_band = in_band;
+        a.coef = dcoef; a.B = B; a.C = C; a.T = T; a.L = (int)L; a.nchunks = nchunks;
+        if (nchunks > 1) {
+            a.out = nullptr; a.proc_tiles = dproc; a.state_in = nullptr; a.state_out = dstate;
+            fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+            NBLS_CUDA(cudaGetLastError());
+            carry_kernel<<<(B * C + 127) / 128, 128, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, S2, rev ? 1 : 0);
+            NBLS_CUDA(cudaGetLastError());
+            ctx->launches += 2;
+        }
+        a.out = y; a.out_row = ldy; a.out_band = ystride_band;
+        a.proc_tiles = nullptr; a.state_in = dstate; a.state_out = nullptr;
+        if (taper) {
+            a.taper_up = dup; a.taper_down = ddown; a.taper_len = d->taper_len; a.g0 = d->global_t0;
+            a.G = d->global_npts > 0 ? d->global_npts : T;
+        }
+        fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        return NBLS_OK;
+    };
+
+    NBLS_CHECK(run_pass(false, x, ldx, 0, !d->zerophase));
+    if (d->zerophase) NBLS_CHECK(run_pass(true, y, ldy, ystride_band, true));
+    return NBLS_OK;
+}
+
+}  // namespace nbls

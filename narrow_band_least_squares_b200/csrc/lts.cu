@@ -1,0 +1,331 @@
+// lts.cu — K3b: FAST-LTS slowness solve with the reference's seeded subset stream, one CTA per
+// band-window, followed by the reweighting step that yields the final outlier flags.
+//
+// Follows lts_array/lts_array/classes/lts_classes.py of the reference:
+//   fast_LTS :58-150 — per window, on standardised data (y = tau/mad, X = xij/xij_mad):
+//     500 starts: exact fit through the 2 pairs drawn by random_set (:16-36; the LCG is restarted
+//     at seed 0 for every window, :76, so the draws are a host-precomputed table), then up to 4
+//     C-steps (rank |r|, keep the h smallest, refit, objective = sum of the h smallest r^2, stop
+//     when the objective repeats, :89-103); the 10 smallest objectives are kept — with duplicates,
+//     because check_array's de-dup never fires (:39-55) — and iterated for up to
+//     100 C-steps (:111-142); the strict minimum wins.
+//   post_process :643-764 (without the uncertainty ellipse): raw scale s0 from the h smallest
+//     squared residuals, first weights |r/s0| <= 2.2414..., refit on them, reweighted scale,
+//     final weights |r/scale| <= 2.5, vel/baz from the refit, sigma_tau over the final weights.
+// A warp runs one start at a time with its lanes spread over the P pairs; ranking is by counting
+// (rank_p = #{q : |r_q| < |r_p| or tie with q < p}), which yields the h-subset and the objective in
+// one pass and makes every fit a deterministic function of the subset.
+#include <float.h>
+#include <math.h>
+#include <math_constants.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "stats.cuh"
+
+namespace nbls {
+
+
+constexpr int LTS_WARPS = 8;
+
+struct LtsArgs {
+    int64_t nwin;
+    int P, h, n_starts, n_keep, csteps1, csteps2;
+    double fs, madx, mady, raw_factor, rew1;
+    const int32_t* lag;
+    const double* cmax;
+    const double* xij;       // [P][2] km
+    const int32_t* subsets;  // [(n_starts+n_keep)][2]
+    const double* rew_cons;  // [P+1]
+    double *mdccm, *mad, *vel, *baz, *sig, *slow;
+    uint8_t* weights;        // [E][P]
+};
+
+struct Sums {
+    double sxx, sxy, syy, sxt, syt, obj;
+};
+
+// 2x2 normal equations -> coefficients; singular systems give NaN (never selected)
+__device__ __forceinline__ void solve2(const Sums& s, double& zx, double& zy) {
+    const double det = s.sxx * s.syy - s.sxy * s.sxy;
+    zx = (s.syy * s.sxt - s.sxy * s.syt) / det;
+    zy = (s.sxx * s.syt - s.sxy * s.sxt) / det;
+}
+
+// One ranking pass for coefficients (zx, zy): residuals, ranks, then over the h smallest |r| the
+// objective and the normal-equation sums of the next fit.  x0/x1/y: [P] shared; absr: warp scratch.
+__device__ __forceinline__ Sums rank_pass(const double* x0, const double* x1, const double* y, double* absr, int P,
+                                          int h, double zx, double zy, int lane) {
+    for (int p = lane; p < P; p += 32) absr[p] = fabs(y[p] - (x0[p] * zx + x1[p] * zy));
+    __syncwarp();
+    Sums s = {0, 0, 0, 0, 0, 0};
+    for (int p = lane; p < P; p += 32) {
+        const double v = absr[p];
+        int rank = 0;
+        for (int q = 0; q < P; ++q) {
+            const double u = absr[q];
+            rank += (u < v) || (u == v && q < p);
+        }
+        if (rank < h) {
+            const double a = x0[p], b = x1[p], t = y[p];
+            s.sxx = fma(a, a, s.sxx); s.sxy = fma(a, b, s.sxy); s.syy = fma(b, b, s.syy);
+            s.sxt = fma(a, t, s.sxt); s.syt = fma(b, t, s.syt);
+            s.obj = fma(v, v, s.obj);
+        }
+    }
+    __syncwarp();
+    s.sxx = warp_sum(s.sxx); s.sxy = warp_sum(s.sxy); s.syy = warp_sum(s.syy);
+    s.sxt = warp_sum(s.sxt); s.syt = warp_sum(s.syt); s.obj = warp_sum(s.obj);
+    return s;
+}
+
+// C-steps from (zx, zy) until the objective repeats or `limit` steps (:89-103 / :125-139)
+__device__ __forceinline__ void csteps(const double* x0, const double* x1, const double* y, double* absr, int P, int h,
+                                       int limit, double& zx, double& zy, double& obj, int lane) {
+    Sums s = rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
+    double prev = 0.0;
+    obj = s.obj;
+    for (int kk = 0; kk < limit; ++kk) {
+        solve2(s, zx, zy);
+        s = rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
+        obj = s.obj;
+        if (kk >= 1 && obj == prev) break;
+        prev = obj;
+    }
+}
+
+// exact fit through two pairs (:84-86); a singular pair of rows gets the minimum-norm solution
+// like LAPACK's lstsq
+__device__ __forceinline__ void fit2(const double* x0, const double* x1, const double* y, int i0, int i1, double& zx,
+                                     double& zy) {
+    const double a = x0[i0], b = x1[i0], c = x0[i1], d = x1[i1], u = y[i0], v = y[i1];
+    const double det = a * d - b * c;
+    if (fabs(det) > 1e-14 * (fabs(a * d) + fabs(b * c))) {
+        zx = (u * d - b * v) / det;
+        zy = (a * v - u * c) / det;
+    } else {
+        const double f = a * a + b * b + c * c + d * d;
+        zx = (a * u + c * v) / f;
+        zy = (b * u + d * v) / f;
+    }
+}
+
+__global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
+    extern __shared__ double sm[];
+    const int P = a.P, NS = a.n_starts, NK = a.n_keep;
+    double* ys = sm;                   // [P] standardised delays
+    double* x0 = ys + P;               // [P]
+    double* x1 = x0 + P;               // [P]
+    double* tau = x1 + P;              // [P] seconds
+    double* scratch = tau + P;         // [LTS_WARPS][P]
+    double* sobj = scratch + (size_t)LTS_WARPS * P;   // [NS]
+    double* szx = sobj + NS;           // [NS]
+    double* szy = szx + NS;            // [NS]
+    double* cobj = szy + NS;           // [NK]
+    double* czx = cobj + NK;           // [NK]
+    double* czy = czx + NK;            // [NK]
+    __shared__ double sh_mdccm, sh_mad;
+    __shared__ int sh_skip, sh_ncand;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    double* absr = scratch + (size_t)warp * P;
+
+    for (int64_t e = blockIdx.x; e < a.nwin; e += gridDim.x) {
+        const int32_t* lag = a.lag + e * P;
+        __syncthreads();
+        if (warp == 0) {
+            double mdccm, mad;
+            const bool skip = window_stats(lag, a.cmax + e * P, P, a.fs, absr, lane, mdccm, mad);
+            if (lane == 0) { sh_mdccm = mdccm; sh_mad = mad; sh_skip = skip ? 1 : 0; sh_ncand = 0; }
+        }
+        __syncthreads();
+        const double mad = sh_mad;
+        const bool skip = sh_skip != 0;
+        if (tid == 0) {
+            if (a.mdccm) a.mdccm[e] = sh_mdccm;
+            if (a.mad) a.mad[e] = mad;
+        }
+        if (skip) {   // data spike (:65-67, :663-665): NaN estimates, all-zero weights
+            if (tid == 0) {
+                if (a.vel) a.vel[e] = qnan();
+                if (a.baz) a.baz[e] = qnan();
+                if (a.sig) a.sig[e] = qnan();
+                if (a.slow) { a.slow[2 * e] = qnan(); a.slow[2 * e + 1] = qnan(); }
+            }
+            if (a.weights) for (int p = tid; p < P; p += blockDim.x) a.weights[e * P + p] = 0;
+            continue;
+        }
+        for (int p = tid; p < P; p += blockDim.x) {
+            const double t = (double)(-lag[p]) / a.fs;
+            tau[p] = t;
+            ys[p] = t / mad;                       // :70
+            x0[p] = a.xij[2 * p] / a.madx;         // xij_standardized (:849-850)
+            x1[p] = a.xij[2 * p + 1] / a.mady;
+        }
+        __syncthreads();
+
+        // ---- 500 random starts (:80-108) ----
+        for (int s = warp; s < NS; s += LTS_WARPS) {
+            double zx, zy, obj;
+            fit2(x0, x1, ys, a.subsets[2 * s], a.subsets[2 * s + 1], zx, zy);
+            csteps(x0, x1, ys, absr, P, a.h, a.csteps1, zx, zy, obj, lane);
+            if (lane == 0) { sobj[s] = obj; szx[s] = zx; szy[s] = zy; }
+        }
+        __syncthreads();
+        // keep the n_keep smallest finite objectives, arrival order on ties
+        for (int s = tid; s < NS; s += blockDim.x) {
+            const double v = sobj[s];
+            if (isfinite(v)) {
+                int rank = 0;
+                for (int q = 0; q < NS; ++q) {
+                    const double u = sobj[q];
+                    rank += isfinite(u) && ((u < v) || (u == v && q < s));
+                }
+                if (rank < NK) { cobj[rank] = v; czx[rank] = szx[s]; czy[rank] = szy[s]; atomicAdd(&sh_ncand, 1); }
+            }
+        }
+        __syncthreads();
+        const int ncand = min(sh_ncand, NK);
+        // ---- final C-steps on the candidates (:111-142) ----
+        for (int c = warp; c < NK; c += LTS_WARPS) {
+            double zx, zy, obj = qnan();
+            bool ok = true;
+            if (c < ncand) { zx = czx[c]; zy = czy[c]; }
+            else {   // fewer than n_keep finite candidates: fresh random pairs (:117-121)
+                const int s = NS + (c - ncand);
+                fit2(x0, x1, ys, a.subsets[2 * s], a.subsets[2 * s + 1], zx, zy);
+            }
+            ok = isfinite(zx);
+            if (ok) csteps(x0, x1, ys, absr, P, a.h, a.csteps2, zx, zy, obj, lane);
+            __syncwarp();
+            if (lane == 0) { cobj[c] = ok ? obj : qnan(); czx[c] = zx; czy[c] = zy; }
+        }
+        __syncthreads();
+
+        // ---- strict minimum, de-standardise (:140-148), post_process (:643-764) : warp 0 ----
+        if (warp == 0) {
+            double best = CUDART_INF, bzx = qnan(), bzy = qnan();
+            for (int c = 0; c < NK; ++c) {
+                const double o = cobj[c];
+                if (o < best) { best = o; bzx = czx[c]; bzy = czy[c]; }
+            }
+            const double cx = bzx * (mad / a.madx), cy = bzy * (mad / a.mady);
+            // raw scale from the h smallest squared residuals (:668-673)
+            for (int p = lane; p < P; p += 32) absr[p] = fabs(tau[p] - (a.xij[2 * p] * cx + a.xij[2 * p + 1] * cy));
+            __syncwarp();
+            double ssq = 0.0;
+            for (int p = lane; p < P; p += 32) {
+                const double v = absr[p];
+                int rank = 0;
+                for (int q = 0; q < P; ++q) {
+                    const double u = absr[q];
+                    rank += (u < v) || (u == v && q < p);
+                }
+                if (rank < a.h) ssq = fma(v, v, ssq);
+            }
+            ssq = warp_sum(ssq);
+            const double s0 = sqrt(ssq / (double)a.h) * a.raw_factor;
+            double zx = cx, zy = cy;
+            // first weights (:679) -> refit (:687-689) -> reweighted scale (:693-700) -> final weights (:701)
+            const bool exact = fabs(s0) < 1e-7;
+            Sums s = {0, 0, 0, 0, 0, 0};
+            int nw = 0;
+            for (int p = lane, i = 0; p < P; p += 32, ++i) {
+                const bool w = exact ? (absr[p] < 1e-7) : (fabs((tau[p] - (a.xij[2 * p] * cx + a.xij[2 * p + 1] * cy)) / s0) <= 2.2414027276049473);
+                if (w) {
+                    const double xa = a.xij[2 * p], xb = a.xij[2 * p + 1], t = tau[p];
+                    s.sxx = fma(xa, xa, s.sxx); s.sxy = fma(xa, xb, s.sxy); s.syy = fma(xb, xb, s.syy);
+                    s.sxt = fma(xa, t, s.sxt); s.syt = fma(xb, t, s.syt);
+                    ++nw;
+                }
+                absr[p] = w ? 1.0 : 0.0;
+            }
+            __syncwarp();
+            nw = __reduce_add_sync(0xffffffffu, nw);
+            if (!exact) {
+                s.sxx = warp_sum(s.sxx); s.sxy = warp_sum(s.sxy); s.syy = warp_sum(s.syy); s.sxt = warp_sum(s.sxt); s.syt = warp_sum(s.syt);
+                solve2(s, zx, zy);
+                double rs = 0.0;
+                for (int p = lane; p < P; p += 32) {
+                    if (absr[p] != 0.0) {
+                        const double r = tau[p] - (a.xij[2 * p] * zx + a.xij[2 * p + 1] * zy);
+                        rs = fma(r, r, rs);
+                    }
+                }
+                rs = warp_sum(rs);
+                double scale = sqrt(rs / (double)(nw - 1)) * a.rew1;
+                if (nw != P) scale *= a.rew_cons[nw];
+                __syncwarp();
+                for (int p = lane; p < P; p += 32) {
+                    const double r = tau[p] - (a.xij[2 * p] * zx + a.xij[2 * p + 1] * zy);
+                    absr[p] = (fabs(r / scale) <= 2.5) ? 1.0 : 0.0;
+                }
+                __syncwarp();
+            }
+            // sigma_tau over the final weights (:723-730)
+            double num = 0.0;
+            int mw = 0;
+            for (int p = lane; p < P; p += 32) {
+                const bool w = absr[p] != 0.0;
+                if (w) {
+                    const double r = tau[p] - (a.xij[2 * p] * zx + a.xij[2 * p + 1] * zy);
+                    num = fma(tau[p], r, num);
+                    ++mw;
+                }
+                if (a.weights) a.weights[e * P + p] = w ? 1 : 0;
+            }
+            num = warp_sum(num);
+            mw = __reduce_add_sync(0xffffffffu, mw);
+            if (lane == 0) {
+                double vel, baz;
+                vel_baz(zx, zy, vel, baz);
+                const double val = num / (double)(mw - 2);
+                const double sig = (val != val || val < 0.0) ? qnan() : sqrt(val);
+                if (a.vel) a.vel[e] = vel;
+                if (a.baz) a.baz[e] = baz;
+                if (a.sig) a.sig[e] = sig;
+                if (a.slow) { a.slow[2 * e] = zx; a.slow[2 * e + 1] = zy; }
+            }
+        }
+    }
+}
+
+int lts_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_t* lag, const double* cmax,
+             const nbls_outputs* out, const double* dgeom) {
+    const int P = s->npairs;
+    NBLS_REQUIRE(s->alpha >= 0.5 && s->alpha < 1.0, "nbls_solve: alpha must lie in [0.5, 1] (got %g)", s->alpha);
+    NBLS_REQUIRE(P >= 4, "nbls_solve: the co-array must have at least 4 elements for least trimmed squares");
+    NBLS_REQUIRE(s->subsets && s->rew_cons, "nbls_solve: LTS tables missing");
+    NBLS_REQUIRE(s->h >= 2 && s->h <= P, "nbls_solve: h=%d out of range", s->h);
+    NBLS_REQUIRE(s->n_starts >= 1 && s->n_starts <= 4096 && s->n_keep >= 1 && s->n_keep <= 64,
+                 "nbls_solve: n_starts/n_keep out of range");
+    const size_t nsub = (size_t)(s->n_starts + s->n_keep) * 2;
+    const size_t tab_bytes = round_up(nsub * sizeof(int32_t), 16) + (size_t)(P + 1) * sizeof(double);
+    NBLS_CHECK(ensure(ctx, ctx->lts_tab, tab_bytes));
+    int32_t* dsub = (int32_t*)ctx->lts_tab.p;
+    double* drew = (double*)((char*)ctx->lts_tab.p + round_up(nsub * sizeof(int32_t), 16));
+    NBLS_CUDA(cudaMemcpyAsync(dsub, s->subsets, nsub * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    NBLS_CUDA(cudaMemcpyAsync(drew, s->rew_cons, (size_t)(P + 1) * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+
+    LtsArgs a;
+    memset(&a, 0, sizeof(a));
+    a.nwin = nwin; a.P = P; a.h = s->h; a.n_starts = s->n_starts; a.n_keep = s->n_keep;
+    a.csteps1 = s->csteps1; a.csteps2 = s->csteps2; a.fs = s->fs;
+    a.madx = s->xij_mad[0]; a.mady = s->xij_mad[1]; a.raw_factor = s->raw_factor; a.rew1 = s->rew_factor1;
+    a.lag = lag; a.cmax = cmax; a.xij = dgeom; a.subsets = dsub; a.rew_cons = drew;
+    a.mdccm = out->mdccm; a.mad = out->mad; a.vel = out->vel; a.baz = out->baz; a.sig = out->sigma_tau;
+    a.slow = out->slowness; a.weights = out->weights;
+    const size_t smem = ((size_t)(4 + LTS_WARPS) * P + 3 * (size_t)s->n_starts + 3 * (size_t)s->n_keep) * sizeof(double);
+    NBLS_REQUIRE(smem <= ctx->smem_optin, "nbls_solve: LTS working set of %zu B exceeds shared memory", smem);
+    NBLS_CUDA(cudaFuncSetAttribute(lts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int grid = (int)std::min<int64_t>(nwin, (int64_t)ctx->sm_count * 32);
+    lts_kernel<<<grid, LTS_WARPS * 32, smem, ctx->stream>>>(a);
+    NBLS_CUDA(cudaGetLastError());
+    ctx->launches += 1;
+    return NBLS_OK;
+}
+
+}  // namespace nbls

@@ -1,0 +1,174 @@
+"""GPU parity: the CUDA path (through the C ABI of libnbls) against the golden fixtures produced by the
+UNMODIFIED reference (tests/golden, oracle/run_reference.py) and against the CPU oracle.
+
+Bars (BASELINE.json north_star): integer lags and LTS outlier flags bit-exact; trace velocity and
+sigma_tau 1e-6 relative; back-azimuth 1e-3 deg; mdccm 1e-9 absolute; NaN pattern identical.
+The filtered samples are compared at 1e-12 of the channel RMS (scipy restatement, parity unpinned
+upstream — SURVEY.md §8(c)).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from narrow_band_least_squares_b200 import _capi
+from narrow_band_least_squares_b200.synth import plane_wave_record
+from oracle import nbls_oracle as orc
+from oracle.run_reference import CASES
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from narrow_band_least_squares_b200.engine import Engine
+    e = Engine(0)
+    yield e
+    e.close()
+
+
+def _load(name):
+    return np.load(os.path.join(GOLD, name + ".npz"), allow_pickle=False)
+
+
+def _case(name):
+    g = _load(name)
+    skw, pkw = CASES[name]
+    rec = plane_wave_record(**skw)
+    tvec = (rec.starttime + np.arange(rec.npts) / rec.fs) / 86400.0
+    return g, rec, tvec, pkw
+
+
+def _close_est(got, ref, what):
+    assert np.array_equal(np.isnan(got), np.isnan(ref)), f"{what}: NaN pattern differs"
+    if what == "baz":
+        d = np.abs(((got - ref + 180.0) % 360.0) - 180.0)
+        assert np.nanmax(d, initial=0.0) <= 1e-3, f"baz differs by {np.nanmax(d)} deg"
+    elif what == "mdccm":
+        assert np.allclose(got, ref, rtol=0, atol=1e-9, equal_nan=True), what
+    else:
+        assert np.allclose(got, ref, rtol=1e-6, atol=1e-12, equal_nan=True), what
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_filter_matches_oracle(eng, name):
+    g, rec, _, pkw = _case(name)
+    fl = g["freqlist"]
+    nb = int(g["nbands"])
+    sos = [orc.design_sos("butter", fl[b], fl[b + 1], rec.fs, int(g["order"])) for b in range(nb)]
+    for kw in (dict(), dict(chunk_len=256, exact_scan=True), dict(chunk_len=1 << 20)):
+        out = eng.filter_bands(rec.data, rec.fs, sos, zerophase=True, **kw)
+        for b in range(nb):
+            ref, _ = orc.filter_record(rec.data, rec.fs, "butter", fl[b], fl[b + 1], int(g["order"]))
+            rms = np.sqrt(np.mean(ref ** 2, axis=1, keepdims=True))
+            rms[rms == 0] = 1.0
+            err = np.max(np.abs(out[b] - ref) / rms)
+            assert err < 1e-12, (name, b, kw, err)
+            if kw.get("chunk_len", 0) >= rec.npts:       # one chunk = scipy's sequential order: bit-exact
+                assert np.array_equal(out[b], ref), (name, b, "single-chunk run must be bit-identical")
+            # fixture cross-check (head/tail samples written by the reference run)
+            assert np.allclose(out[b][:, :64], g[f"b{b}_filt_head"], rtol=0, atol=1e-12 * float(rms.max()))
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_xcorr_lags_bit_exact(eng, name):
+    g, rec, _, pkw = _case(name)
+    fl, wl = g["freqlist"], g["winlen_list"]
+    nb = int(g["nbands"])
+    filt = np.stack([orc.filter_record(rec.data, rec.fs, "butter", fl[b], fl[b + 1], int(g["order"]))[0]
+                     for b in range(nb)])
+    n = [int(g[f"b{b}_winlensamp"]) for b in range(nb)]
+    hop = [int(g[f"b{b}_sampinc"]) for b in range(nb)]
+    cnt = [len(g[f"b{b}_intervals"]) for b in range(nb)]
+    lag, cmax = eng.xcorr(filt, n, hop, cnt, method=_capi.XCORR_DIRECT)
+    row = 0
+    for b in range(nb):
+        r = slice(row, row + cnt[b])
+        assert np.array_equal(lag[r].T, g[f"b{b}_lag"]), (name, b, "integer lags must match the reference exactly")
+        assert np.allclose(cmax[r].T, g[f"b{b}_cmax"], rtol=0, atol=1e-12, equal_nan=True)
+        row += cnt[b]
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_solve_matches_reference(eng, name):
+    g, rec, _, pkw = _case(name)
+    alpha = float(g["alpha"])
+    for b in range(int(g["nbands"])):
+        lag = np.ascontiguousarray(g[f"b{b}_lag"].T)
+        cmax = np.ascontiguousarray(g[f"b{b}_cmax"].T)
+        out = eng.solve(lag, cmax, g["b0_rij"], rec.fs, alpha)
+        _close_est(out["mdccm"], g[f"b{b}_mdccm"], "mdccm")
+        assert np.array_equal(out["mad"], g[f"b{b}_mad"])
+        _close_est(out["vel"], g[f"b{b}_vel"], "vel")
+        _close_est(out["baz"], g[f"b{b}_baz"], "baz")
+        _close_est(out["sigma_tau"], g[f"b{b}_sigma_tau"], "sigma_tau")
+        if alpha != 1.0:
+            assert np.array_equal(out["weights"].T, g[f"b{b}_element_weights"]), (name, b, "LTS flags must match exactly")
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_driver_matches_reference_driver(eng, name):
+    from narrow_band_least_squares_b200 import narrow_band_least_squares
+    g, rec, tvec, pkw = _case(name)
+    nb = int(g["nbands"])
+    frl = g["nbls_freq_resp_list"]
+    out = narrow_band_least_squares(list(g["winlen_list"]), float(g["winover"]), float(g["alpha"]),
+                                    (rec.data, rec.fs, tvec), rec.lat, rec.lon, nb, np.zeros(50), np.zeros(50, complex),
+                                    g["freqlist"], "log", frl, "butter", int(g["order"]), 0.01, rij=g["b0_rij"], engine=eng,
+                                    return_details=True)
+    (vel, baz, md, tt, stdict_all, sig, ncl, w_arr, h_arr), plan, res = out
+    assert ncl == g["nbls_num_compute"].tolist()
+    assert vel.shape == g["nbls_vel"].shape
+    _close_est(vel, g["nbls_vel"], "vel")
+    _close_est(baz, g["nbls_baz"], "baz")
+    _close_est(md, g["nbls_mdccm"], "mdccm")
+    assert np.array_equal(tt, g["nbls_t"], equal_nan=True)
+    assert np.array_equal(w_arr, g["nbls_w"]) and np.array_equal(h_arr, g["nbls_h"])
+    for b in range(nb):       # end-to-end lags (GPU-filtered input) against the reference's
+        assert np.array_equal(res.band(b)["lag"], g[f"b{b}_lag"]), (name, b)
+    if float(g["alpha"]) == 1.0:
+        _close_est(sig, g["nbls_sig_tau"], "sigma_tau")
+        assert stdict_all is None
+    else:
+        keys = [k for k in stdict_all if k != "size"]
+        assert keys == [str(k) for k in g["nbls_stdict_keys"]]
+        off = g["nbls_stdict_off"]
+        for i, k in enumerate(keys):
+            assert np.array_equal(stdict_all[k], g["nbls_stdict_vals"][off[i]:off[i + 1]])
+        assert stdict_all["size"] == int(g["nbls_stdict_size"])
+
+
+def test_ltsva_surface_and_restricted_lag(eng):
+    from narrow_band_least_squares_b200 import ltsva
+    g, rec, tvec, pkw = _case("g2_lts_c6")
+    fl = g["freqlist"]
+    filt, _ = orc.filter_record(rec.data, rec.fs, "butter", fl[0], fl[1], int(g["order"]))
+    vel, baz, t, md, stdict, sig, civ, cib = ltsva((filt, rec.fs, tvec), rec.lat, rec.lon, float(g["winlen_list"][0]),
+                                                   float(g["winover"]), float(g["alpha"]), rij=g["b0_rij"], engine=eng)
+    _close_est(vel, g["b0_vel"], "vel")
+    _close_est(baz, g["b0_baz"], "baz")
+    assert np.array_equal(t, g["b0_t"])
+    keys = [k for k in stdict if k != "size"]
+    assert keys == [str(k) for k in g["b0_stdict_keys"]] and stdict["size"] == rec.nchans
+    assert np.all(np.isnan(civ)) and np.all(np.isnan(cib))
+    # restricted lag search against the oracle's sliced arg-max
+    L = 150
+    n, hop, starts = orc.window_grid(rec.npts, rec.fs, float(g["winlen_list"][0]), float(g["winover"]))
+    pairs, *_ = orc.co_array(g["b0_rij"])
+    ref_lag, ref_cmax, *_ = orc.correlate_windows(np.ascontiguousarray(filt.T), starts, n, rec.fs, pairs, None, L)
+    lag, cmax = eng.xcorr(filt[None], [n], [hop], [len(starts)], max_lag=L, method=_capi.XCORR_DIRECT)
+    assert np.array_equal(lag.T, ref_lag)
+    assert np.allclose(cmax.T, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
+
+
+def test_errors_mirror_reference(eng):
+    from narrow_band_least_squares_b200 import ltsva
+    x = np.random.default_rng(0).standard_normal((2, 4000))
+    with pytest.raises(RuntimeError):
+        ltsva((x, 40.0), None, None, 10.0, 0.5, rij=np.array([[0.0, 1.0], [0.0, 0.5]]), engine=eng)
+    x = np.random.default_rng(0).standard_normal((3, 4000))
+    with pytest.raises(RuntimeError):     # LTS needs a co-array of >= 4
+        ltsva((x, 40.0), None, None, 10.0, 0.5, 0.75, rij=np.array([[0.0, 1.0, 0.3], [0.0, 0.5, 0.9]]), engine=eng)
+    with pytest.raises(RuntimeError):     # collinear array: rank-deficient co-array
+        ltsva((x, 40.0), None, None, 10.0, 0.5, rij=np.array([[0.0, 1.0, 2.0], [0.0, 1.0, 2.0]]), engine=eng)
