@@ -39,11 +39,6 @@ int ensure(nbls_ctx* ctx, DevBuf& b, size_t bytes) {
     return NBLS_OK;
 }
 
-int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                      int max_lag, int32_t* lag, double* cmax);
-int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                   int max_lag, int32_t* lag, double* cmax);
-bool xcorr_fft_supported(nbls_ctx* ctx, int N);
 
 static int validate_windows(const nbls_window_desc* w, int C, int64_t ldy, int64_t* total) {
     NBLS_REQUIRE(w && w->win_len && w->win_hop && w->win_first && w->win_count, "nbls_xcorr: null window arrays");
@@ -73,8 +68,10 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
     for (int b = 0; b < w->nbands; ++b) {
         const int N = w->win_len[b], W = w->win_count[b];
         int method = w->method;
-        if (method == NBLS_XCORR_AUTO) method = NBLS_XCORR_DIRECT;
-        if (method == NBLS_XCORR_FFT && !xcorr_fft_supported(ctx, N)) {
+        // AUTO: the FFT path wherever it applies and the window is long enough for N log N to win
+        if (method == NBLS_XCORR_AUTO)
+            method = (N >= 128 && xcorr_fft_length(N, w->max_lag) > 0) ? NBLS_XCORR_FFT : NBLS_XCORR_DIRECT;
+        if (method == NBLS_XCORR_FFT && xcorr_fft_length(N, w->max_lag) == 0) {
             set_error("nbls_xcorr: FFT path does not support windows of %d samples", N);
             return NBLS_ERR_UNSUPPORTED;
         }
@@ -84,17 +81,11 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
         if (method == NBLS_XCORR_FFT)
             NBLS_CHECK(xcorr_fft_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb));
         else
-            NBLS_CHECK(xcorr_direct_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb));
+            NBLS_CHECK(xcorr_direct_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb,
+                                         nullptr, nullptr, 0));
         row += W;
     }
     return NBLS_OK;
-}
-
-// placeholder until the FFT path lands
-bool xcorr_fft_supported(nbls_ctx*, int) { return false; }
-int xcorr_fft_band(nbls_ctx*, const double*, int64_t, int, int, int, int64_t, int, int, int32_t*, double*) {
-    set_error("nbls_xcorr: FFT path not built");
-    return NBLS_ERR_UNSUPPORTED;
 }
 
 // ---- FP64 FMA peak microbenchmark ---------------------------------------------------------
@@ -263,9 +254,12 @@ int nbls_destroy(nbls_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->coef, &ctx->state, &ctx->carry, &ctx->taper, &ctx->filt, &ctx->geom, &ctx->lts_tab,
-                      &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch};
+                      &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch, &ctx->spec,
+                      &ctx->energy, &ctx->flags};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
+    for (auto& kv : ctx->fft_tw)
+        if (kv.second) cudaFree(kv.second);
     for (int i = 0; i < EV_COUNT; ++i)
         if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     cudaStreamDestroy(ctx->stream);

@@ -5,6 +5,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <map>
 #include <string>
 #include <vector>
 
@@ -57,6 +58,8 @@ struct nbls_ctx {
     int64_t launches = 0;
     // cached buffers
     nbls::DevBuf coef, state, carry, taper, filt, geom, lts_tab, xin, res, lagbuf, cmaxbuf, wbuf, scratch;
+    nbls::DevBuf spec, energy, flags;       // FFT cross-correlation workspace
+    std::map<int, void*> fft_tw;            // twiddle tables by transform length (device)
     cudaEvent_t ev[nbls::EV_COUNT] = {};
     bool ev_valid = false;
     float stage_ms[6] = {};
@@ -74,6 +77,12 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
 int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_t* lag,
                const double* cmax, const nbls_outputs* out);
 int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
+int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
+                      int max_lag, int32_t* lag, double* cmax, const int* list, const int* count, int grid_cap);
+int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
+                   int max_lag, int32_t* lag, double* cmax);
+// transform length the FFT path would use for a window of N samples and lag bound, 0 if unsupported
+int xcorr_fft_length(int N, int max_lag);
 
 static inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 

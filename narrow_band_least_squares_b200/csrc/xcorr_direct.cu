@@ -44,6 +44,8 @@ struct XcArgs {
     int wt_hi0;
     int32_t* lag;         // [W][P]
     double* cmax;         // [W][P] or nullptr
+    const int* list;      // list mode: items w*P+p to evaluate (device), else nullptr = every (w, p)
+    const int* count;     // list mode: number of items (device)
 };
 
 __device__ __forceinline__ int pad_b(int e) { return e + ((e >> 3) << 1); }
@@ -65,7 +67,11 @@ __global__ void __launch_bounds__(XC_MAX_WARPS * 32, 1) xcorr_direct_kernel(XcAr
     __shared__ int red_l[XC_MAX_WARPS];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
-    const int w = blockIdx.x / g.P, p = blockIdx.x - w * g.P;
+    // one (window, pair) per CTA; in list mode a CTA strides over the items listed on the device
+    const int64_t n_items = g.list ? (int64_t)*g.count : (int64_t)gridDim.x;
+    for (int64_t item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int64_t wp = g.list ? (int64_t)g.list[item] : item;
+    const int w = (int)(wp / g.P), p = (int)(wp - (int64_t)w * g.P);
     // pair index -> (i, j), i<j row-major (lts_classes.py:840)
     int ci = 0, rem = p;
     while (rem >= g.C - 1 - ci) { rem -= g.C - 1 - ci; ++ci; }
@@ -186,16 +192,21 @@ __global__ void __launch_bounds__(XC_MAX_WARPS * 32, 1) xcorr_direct_kernel(XcAr
         g.lag[o] = dead ? -g.lag_max : best.lag;
         if (g.cmax) g.cmax[o] = dead ? __longlong_as_double(0x7ff8000000000000LL) : best.v / den;
     }
+    __syncthreads();   // shared buffers are reused by the next item
+    }
 }
 
+// list == nullptr: every (window, pair) of the band.  Otherwise only the items w*P+p in list[0..*count)
+// (both on the device; used by the FFT path to settle near-tied arg-maxima), with at most `grid_cap` CTAs.
 int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                      int max_lag, int32_t* lag, double* cmax) {
+                      int max_lag, int32_t* lag, double* cmax, const int* list, const int* count, int grid_cap) {
     if (W <= 0) return NBLS_OK;
     const int P = C * (C - 1) / 2;
     XcArgs a;
     memset(&a, 0, sizeof(a));
     a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.M = (int)round_up(N, 8);
     a.hop = hop; a.first = first; a.W = W; a.lag = lag; a.cmax = cmax;
+    a.list = list; a.count = count;
     a.lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
     const int WT = (a.M + 255) / 256;                       // warp-tiles of 256 slots
     const int lo_last = a.lag_max / 256;                    // warp-tiles holding lags 0..lag_max
@@ -212,7 +223,7 @@ int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, in
         return NBLS_ERR_UNSUPPORTED;
     }
     NBLS_CUDA(cudaFuncSetAttribute(xcorr_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t nblocks = (int64_t)W * P;
+    const int64_t nblocks = list ? std::min<int64_t>((int64_t)W * P, std::max(1, grid_cap)) : (int64_t)W * P;
     NBLS_REQUIRE(nblocks < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld", (long long)nblocks);
     xcorr_direct_kernel<<<(unsigned)nblocks, nwarps * 32, smem, ctx->stream>>>(a);
     NBLS_CUDA(cudaGetLastError());

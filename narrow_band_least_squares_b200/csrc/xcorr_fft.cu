@@ -1,0 +1,487 @@
+// xcorr_fft.cu — K2 (frequency domain): windowed pairwise cross-correlation over the co-array through
+// shared-memory FP64 FFTs, with an on-chip arg-max and an exactness guard.
+//
+// Replaces LsBeam.correlate (lts_array/lts_array/classes/lts_classes.py:852-880 of the reference):
+// cij = np.correlate(x_i, x_j, 'full') / sqrt(Ei*Ej); delay = argmax(cij); cmax = max(cij).
+// np.correlate costs N^2 multiply-adds per pair-window; here a window of N samples is zero-padded to
+// L >= N + lag_max (L = R1*R2*R3 with factors 2 and 3) and
+//   spectra kernel : one CTA per (window, channel pair): both channels, scaled to unit energy, ride in
+//                    one complex FFT (z = x_a + i x_b); the two half-spectra are unpacked and stored.
+//   pair kernel    : one CTA per (window, two co-array pairs): Z = X_i1 conj(X_j1) + i X_i2 conj(X_j2)
+//                    is built on the fly while loading, one inverse complex FFT returns the two
+//                    correlation functions in its real and imaginary parts, and the arg-max over the
+//                    wanted lags is taken from registers — the correlation function never exists in
+//                    memory.
+// FFT structure (both kernels): three register-radix passes R1, R2, R3 with two exchanges through a
+// padded shared-memory array; pass 1 of the pair kernel handles the butterflies f0 and M1-f0
+// together because the Hermitian halves Z[f], Z[L-f] come from the same spectrum entries.
+//
+// Exactness guard: the FFT value of a lag differs from the exact sum by far less than TAU (in units
+// of the normalised correlation).  Each thread tracks the best and the second-best value; if the
+// two best lags of a pair are closer than TAU the arg-max is not decided here — the pair-window is
+// appended to a list and re-evaluated by the time-domain FP64 kernel (xcorr_direct.cu, list mode),
+// whose first-maximum-wins semantics match np.argmax.  For every other pair-window the FFT arg-max
+// provably equals the time-domain one.
+#include <float.h>
+#include <limits.h>
+#include <math.h>
+#include <math_constants.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+#include <vector>
+
+#include "common.cuh"
+#include "fft_radix.cuh"
+
+namespace nbls {
+
+using namespace fft;
+
+constexpr double XF_TAU = 1e-10;   // near-tie threshold, normalised correlation units
+
+struct XfArgs {
+    const double* y;      // band base, [C] rows of stride ldy
+    int64_t ldy;
+    int C, P;
+    int N, hop;
+    int64_t first;        // sample index of window 0 of the band
+    int w0, wn;           // windows [w0, w0+wn) of the band are processed by this launch
+    int lag_max;
+    int SP;               // spectrum row length L/2+1
+    const double2* tw;    // [L] e^{+2 pi i k/L}
+    double2* spec;        // [wn][C][SP]
+    double* energy;       // [wn][C]
+    int32_t* lag;         // [W][P] band level
+    double* cmax;         // [W][P] or nullptr
+    int* flag_list;       // [>= wn*P] items w*P+p (band level) to re-evaluate in the time domain
+    int* flag_count;
+};
+
+template <int R1_, int R2_, int R3_>
+struct Shape {
+    static constexpr int R1 = R1_, R2 = R2_, R3 = R3_;
+    static constexpr int L = R1 * R2 * R3;
+    static constexpr int M1 = R2 * R3;              // length of the sub-transforms after pass 1
+    static constexpr int M2 = R3;                   // ... after pass 2
+    static constexpr int ROW = R3 + 1;              // padded block stride: one spare slot per R3
+    static constexpr int SMEM_ELEMS = ROW * R1 * R2;
+    // position of natural index i (pass-1 output order n1*M1 + f) in the padded array
+    static __device__ __forceinline__ int pad(int i) { return i + i / R3; }
+    // position of output index n after the in-place pass 3
+    static __device__ __forceinline__ int pos(int n) {
+        return ROW * ((n % R1) * R2 + (n / R1) % R2) + n / (R1 * R2);
+    }
+};
+
+__device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
+
+// pass 1 tail: radix-R1 butterfly of the inputs f0 + M1*k, twiddle from the table, store
+template <class S>
+__device__ __forceinline__ void pass1_table(double2 (&z)[S::R1], int f0, double2* sm, const double2* tw) {
+    Dft<S::R1>::run(z);
+#pragma unroll
+    for (int n1 = 0; n1 < S::R1; ++n1) {
+        const double2 v = n1 == 0 ? z[0] : cmul(z[n1], ldg2(tw + f0 * n1));
+        sm[S::pad(n1 * S::M1 + f0)] = v;
+    }
+}
+
+// pass 2: radix-R2 butterflies inside every sub-transform, in place
+template <class S, int T>
+__device__ __forceinline__ void pass2(double2* sm, const double2* tw, int tid) {
+    for (int u = tid; u < S::L / S::R2; u += T) {
+        const int n1 = u / S::M2, f1 = u - n1 * S::M2;
+        double2* base = sm + S::ROW * (n1 * S::R2) + f1;
+        double2 z[S::R2];
+#pragma unroll
+        for (int k = 0; k < S::R2; ++k) z[k] = base[S::ROW * k];
+        Dft<S::R2>::run(z);
+        const double2* t = tw + S::R1 * f1;          // w_L^{R1 f1 n2}
+#pragma unroll
+        for (int n2 = 0; n2 < S::R2; ++n2) {
+            const double2 v = n2 == 0 ? z[0] : cmul(z[n2], ldg2(t + (S::R1 * f1) * (n2 - 1)));
+            base[S::ROW * n2] = v;
+        }
+    }
+}
+
+// ---- spectra kernel -------------------------------------------------------------------------
+// grid = wn * ceil(C/2); CTA (w, cp) transforms channels a = 2cp and b = 2cp+1 of window w.
+// Forward DFT through the inverse machinery: Y = IDFT(conj z)  =>  Z = conj(Y).
+template <class S, int T>
+__global__ void __launch_bounds__(T) xf_spectra_kernel(XfArgs g) {
+    extern __shared__ __align__(16) double2 xf_smem[];
+    double2* sm = xf_smem;
+    __shared__ double red[2][T / 32];
+    __shared__ double rs_sh[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ncp = (g.C + 1) >> 1;
+    const int wl = blockIdx.x / ncp, cp = blockIdx.x - wl * ncp;
+    const int ca = 2 * cp, cb = 2 * cp + 1;
+    const bool has_b = cb < g.C;
+    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+    const double* xa = g.y + (int64_t)ca * g.ldy + t0;
+    const double* xb = g.y + (int64_t)(has_b ? cb : ca) * g.ldy + t0;
+
+    // energies (same accumulation as the time-domain kernel: strided fma, then tree)
+    double ea = 0.0, eb = 0.0;
+    for (int n = tid; n < g.N; n += T) {
+        const double va = xa[n], vb = xb[n];
+        ea = fma(va, va, ea);
+        eb = fma(vb, vb, eb);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ea += __shfl_xor_sync(0xffffffffu, ea, o);
+        eb += __shfl_xor_sync(0xffffffffu, eb, o);
+    }
+    if (lane == 0) { red[0][warp] = ea; red[1][warp] = eb; }
+    __syncthreads();
+    if (tid == 0) {
+        double Ea = 0.0, Eb = 0.0;
+        for (int i = 0; i < T / 32; ++i) { Ea += red[0][i]; Eb += red[1][i]; }
+        if (!has_b) Eb = 0.0;
+        g.energy[(int64_t)wl * g.C + ca] = Ea;
+        if (has_b) g.energy[(int64_t)wl * g.C + cb] = Eb;
+        // unit-energy scaling keeps both riders of a packed transform at the same magnitude
+        rs_sh[0] = (Ea > 0.0 && isfinite(Ea)) ? 1.0 / sqrt(Ea) : 0.0;
+        rs_sh[1] = (Eb > 0.0 && isfinite(Eb)) ? 1.0 / sqrt(Eb) : 0.0;
+    }
+    __syncthreads();
+    const double rsa = rs_sh[0], rsb = rs_sh[1];
+
+    // pass 1: inputs conj(z)[n] = (x_a[n], -x_b[n]) * scale, zero beyond the window
+    for (int f0 = tid; f0 < S::M1; f0 += T) {
+        double2 z[S::R1];
+#pragma unroll
+        for (int k = 0; k < S::R1; ++k) {
+            const int n = f0 + S::M1 * k;
+            z[k] = n < g.N ? make_double2(xa[n] * rsa, -(xb[n] * rsb)) : make_double2(0.0, 0.0);
+        }
+        pass1_table<S>(z, f0, sm, g.tw);
+    }
+    __syncthreads();
+    pass2<S, T>(sm, g.tw, tid);
+    __syncthreads();
+    // pass 3 in place
+    for (int u = tid; u < S::L / S::R3; u += T) {
+        double2* base = sm + S::ROW * u;
+        double2 z[S::R3];
+#pragma unroll
+        for (int k = 0; k < S::R3; ++k) z[k] = base[k];
+        Dft<S::R3>::run(z);
+#pragma unroll
+        for (int k = 0; k < S::R3; ++k) base[k] = z[k];
+    }
+    __syncthreads();
+    // unpack: X_a[f] = (conj(Y[f]) + Y[L-f]) / 2,  X_b[f] = (conj(Y[f]) - Y[L-f]) / (2i)
+    double2* Xa = g.spec + ((int64_t)wl * g.C + ca) * g.SP;
+    double2* Xb = g.spec + ((int64_t)wl * g.C + cb) * g.SP;
+    for (int f = tid; f <= S::L / 2; f += T) {
+        const double2 yf = sm[S::pos(f)];
+        const double2 ym = sm[S::pos(f == 0 ? 0 : S::L - f)];
+        Xa[f] = make_double2(0.5 * (yf.x + ym.x), 0.5 * (ym.y - yf.y));
+        if (has_b) Xb[f] = make_double2(-0.5 * (yf.y + ym.y), -0.5 * (yf.x - ym.x));
+    }
+}
+
+// ---- pair kernel ----------------------------------------------------------------------------
+struct Top {       // best and second-best value seen, lag of the best
+    double b1, b2;
+    int l1;
+};
+__device__ __forceinline__ void top_push(Top& t, double v, int lag) {
+    const bool p1 = v > t.b1, p2 = v > t.b2;
+    t.b2 = p1 ? t.b1 : (p2 ? v : t.b2);
+    t.b1 = p1 ? v : t.b1;
+    t.l1 = p1 ? lag : t.l1;
+}
+__device__ __forceinline__ void top_merge(Top& a, double b1, double b2, int l1) {
+    if (b1 > a.b1) {
+        a.b2 = fmax(a.b1, b2);
+        a.b1 = b1;
+        a.l1 = l1;
+    } else {
+        a.b2 = fmax(a.b2, b1);     // an exact tie lands here: gap 0 -> decided in the time domain
+    }
+}
+__device__ __forceinline__ void pair_channels(int p, int C, int& ci, int& cj) {
+    int i = 0, rem = p;            // i<j row-major (lts_classes.py:840)
+    while (rem >= C - 1 - i) { rem -= C - 1 - i; ++i; }
+    ci = i;
+    cj = i + 1 + rem;
+}
+
+// pass-1 stores of the partner butterflies f0 = t (A) and M1 - t (B); W[n] = w_L^{t n}, so B's twiddle
+// is w_L^{(M1-t) n} = e^{2 pi i n/R1} conj(W[n])
+template <class S, int N1>
+__device__ __forceinline__ void store_pair(const double2 (&zA)[S::R1], const double2 (&zB)[S::R1],
+                                           const double2 (&W)[S::R1], int t, double2* sm) {
+    if constexpr (N1 < S::R1) {
+        if constexpr (N1 == 0) {
+            sm[S::pad(t)] = zA[0];
+            sm[S::pad(S::M1 - t)] = zB[0];
+        } else {
+            sm[S::pad(N1 * S::M1 + t)] = cmul(zA[N1], W[N1]);
+            sm[S::pad(N1 * S::M1 + S::M1 - t)] = cmul(zB[N1], mul_root<N1, S::R1>(cconj(W[N1])));
+        }
+        store_pair<S, N1 + 1>(zA, zB, W, t, sm);
+    }
+}
+
+// grid = wn * ceil(P/2); CTA (w, q) correlates pairs 2q (real part) and 2q+1 (imaginary part)
+template <class S, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
+    extern __shared__ __align__(16) double2 xf_smem[];
+    double2* sm = xf_smem;
+    __shared__ double rb1[2][T / 32], rb2[2][T / 32];
+    __shared__ int rl1[2][T / 32];
+    constexpr int R1 = S::R1, L = S::L, M1 = S::M1;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int npp = (g.P + 1) >> 1;
+    const int wl = blockIdx.x / npp, q = blockIdx.x - wl * npp;
+    const int p0 = 2 * q, p1 = 2 * q + 1;
+    const bool has1 = p1 < g.P;
+    int i0, j0, i1, j1;
+    pair_channels(p0, g.C, i0, j0);
+    pair_channels(has1 ? p1 : p0, g.C, i1, j1);
+    const double2* sbase = g.spec + (int64_t)wl * g.C * g.SP;
+    const double2 *Xi0 = sbase + (int64_t)i0 * g.SP, *Xj0 = sbase + (int64_t)j0 * g.SP;
+    const double2 *Xi1 = sbase + (int64_t)i1 * g.SP, *Xj1 = sbase + (int64_t)j1 * g.SP;
+    const bool same_i = i0 == i1;
+
+    // cross-spectra of entry gidx: a = X_i0 conj(X_j0), b = X_i1 conj(X_j1)
+    auto cross = [&](int gidx, double2& a, double2& b) {
+        const double2 xi = ldg2(Xi0 + gidx);
+        a = cmulc(xi, ldg2(Xj0 + gidx));
+        if (has1) b = cmulc(same_i ? xi : ldg2(Xi1 + gidx), ldg2(Xj1 + gidx));
+        else b = make_double2(0.0, 0.0);
+    };
+    // Z[f] for any f in [0, L): Z = a + i b on the stored half, conj(a) + i conj(b) on the mirrored one
+    auto fetch = [&](int f) -> double2 {
+        double2 a, b;
+        if (f <= L / 2) { cross(f, a, b); return make_double2(a.x - b.y, a.y + b.x); }
+        cross(L - f, a, b);
+        return make_double2(a.x + b.y, b.x - a.y);
+    };
+
+    // ---- pass 1: task t owns the butterflies f0 = t and M1 - t (Hermitian partners) ----
+    for (int t = tid; t < M1 / 2; t += T) {
+        if (t == 0) {      // the two self-mirrored butterflies f0 = 0 and f0 = M1/2
+            double2 z[R1];
+#pragma unroll
+            for (int k = 0; k < R1; ++k) z[k] = fetch(M1 * k);
+            pass1_table<S>(z, 0, sm, g.tw);
+#pragma unroll
+            for (int k = 0; k < R1; ++k) z[k] = fetch(M1 / 2 + M1 * k);
+            pass1_table<S>(z, M1 / 2, sm, g.tw);
+            continue;
+        }
+        double2 zA[R1], zB[R1];
+#pragma unroll
+        for (int k = 0; k < R1; ++k) {
+            // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd)
+            constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
+            const bool direct = k < HALF;
+            const int f = t + M1 * k;
+            double2 a, b;
+            cross(direct ? f : L - f, a, b);
+            const double2 zg = make_double2(a.x - b.y, a.y + b.x);     // Z[g]
+            const double2 zm = make_double2(a.x + b.y, b.x - a.y);     // Z[L-g]
+            zA[k] = direct ? zg : zm;
+            zB[R1 - 1 - k] = direct ? zm : zg;
+        }
+        Dft<R1>::run(zA);
+        Dft<R1>::run(zB);
+        double2 W[R1];
+        W[0] = make_double2(1.0, 0.0);
+        if constexpr (R1 > 1) W[1] = ldg2(g.tw + t);
+        powers<R1>(W);
+        store_pair<S, 0>(zA, zB, W, t, sm);
+    }
+    __syncthreads();
+    pass2<S, T>(sm, g.tw, tid);
+    __syncthreads();
+
+    // ---- pass 3 + arg-max straight from registers ----
+    Top tr = {-CUDART_INF, -CUDART_INF, INT_MAX}, ti = {-CUDART_INF, -CUDART_INF, INT_MAX};
+    const int lag_max = g.lag_max;
+    for (int u = tid; u < L / S::R3; u += T) {
+        const double2* base = sm + S::ROW * u;
+        double2 z[S::R3];
+#pragma unroll
+        for (int k = 0; k < S::R3; ++k) z[k] = base[k];
+        Dft<S::R3>::run(z);
+        const int n1 = u / S::R2, n2 = u - n1 * S::R2;
+        const int nb = n1 + R1 * n2;
+#pragma unroll
+        for (int n3 = 0; n3 < S::R3; ++n3) {
+            const int n = nb + R1 * S::R2 * n3;            // circular index: lag n, or n - L
+            const int lag = n <= lag_max ? n : n - L;
+            const bool ok = (n <= lag_max) || (n >= L - lag_max);
+            top_push(tr, ok ? z[n3].x : -CUDART_INF, lag);
+            top_push(ti, ok ? z[n3].y : -CUDART_INF, lag);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        top_merge(tr, __shfl_xor_sync(0xffffffffu, tr.b1, o), __shfl_xor_sync(0xffffffffu, tr.b2, o),
+                  __shfl_xor_sync(0xffffffffu, tr.l1, o));
+        top_merge(ti, __shfl_xor_sync(0xffffffffu, ti.b1, o), __shfl_xor_sync(0xffffffffu, ti.b2, o),
+                  __shfl_xor_sync(0xffffffffu, ti.l1, o));
+    }
+    if (lane == 0) {
+        rb1[0][warp] = tr.b1; rb2[0][warp] = tr.b2; rl1[0][warp] = tr.l1;
+        rb1[1][warp] = ti.b1; rb2[1][warp] = ti.b2; rl1[1][warp] = ti.l1;
+    }
+    __syncthreads();
+    if (tid < 2 && (tid == 0 || has1)) {
+        Top b = {rb1[tid][0], rb2[tid][0], rl1[tid][0]};
+        for (int i = 1; i < T / 32; ++i) top_merge(b, rb1[tid][i], rb2[tid][i], rl1[tid][i]);
+        const int p = tid == 0 ? p0 : p1;
+        const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
+        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
+        const double den = sqrt(Ei * Ej);
+        const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+        if (!(den > 0.0)) {
+            // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched
+            g.lag[item] = -lag_max;
+            if (g.cmax) g.cmax[item] = __longlong_as_double(0x7ff8000000000000LL);
+        } else {
+            g.lag[item] = b.l1 == INT_MAX ? -lag_max : b.l1;
+            if (g.cmax) g.cmax[item] = b.b1 / (double)L;
+            // undecided (near-tie, or non-finite data): the time-domain kernel settles it
+            if (!(b.b1 - b.b2 > XF_TAU * (double)L) || !isfinite(den)) {
+                const int slot = atomicAdd(g.flag_count, 1);
+                g.flag_list[slot] = (int)item;
+            }
+        }
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------
+typedef void (*xf_kernel)(XfArgs);
+struct XfPlan {
+    int L, threads;
+    size_t smem;
+    xf_kernel spectra, pair;
+};
+
+template <int R1, int R2, int R3, int T, int MINB>
+static XfPlan make_plan() {
+    using S = Shape<R1, R2, R3>;
+    XfPlan p;
+    p.L = S::L;
+    p.threads = T;
+    p.smem = (size_t)S::SMEM_ELEMS * sizeof(double2);
+    p.spectra = xf_spectra_kernel<S, T>;
+    p.pair = xf_pair_kernel<S, T, MINB>;
+    return p;
+}
+
+// transform lengths 2^a and 3*2^a from 512 to 12288 (192 KB of complex FP64 is what one SM holds)
+static const std::vector<XfPlan>& plans() {
+    static const std::vector<XfPlan> v = {
+        make_plan<2, 16, 16, 32, 4>(),   make_plan<3, 16, 16, 64, 4>(),   make_plan<4, 16, 16, 64, 4>(),
+        make_plan<6, 16, 16, 96, 4>(),   make_plan<8, 16, 16, 128, 3>(),  make_plan<12, 16, 16, 192, 2>(),
+        make_plan<16, 16, 16, 256, 2>(), make_plan<6, 32, 32, 192, 2>(),  make_plan<8, 32, 32, 256, 1>(),
+        make_plan<12, 32, 32, 384, 1>(),
+    };
+    return v;
+}
+
+static const XfPlan* pick_plan(int N, int max_lag) {
+    if (N < 1) return nullptr;
+    const int lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
+    const int need = N + lag_max;          // circular length with no wrap-around inside |lag| <= lag_max
+    for (const XfPlan& p : plans())
+        if (p.L >= need) return &p;
+    return nullptr;
+}
+
+int xcorr_fft_length(int N, int max_lag) {
+    const XfPlan* p = pick_plan(N, max_lag);
+    return p ? p->L : 0;
+}
+
+static int twiddles(nbls_ctx* ctx, int L, const double2** out) {
+    auto it = ctx->fft_tw.find(L);
+    if (it != ctx->fft_tw.end()) { *out = (const double2*)it->second; return NBLS_OK; }
+    std::vector<double2> h(L);
+    const long double two_pi = 6.283185307179586476925286766559005768L;
+    for (int k = 0; k < L; ++k) {
+        // reduce to the first octant so that symmetric entries are exact mirror images
+        const long double a = two_pi * (long double)k / (long double)L;
+        h[k] = make_double2((double)cosl(a), (double)sinl(a));
+    }
+    void* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, (size_t)L * sizeof(double2));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("nbls_xcorr(fft): twiddle table allocation failed: %s", cudaGetErrorString(e));
+        return NBLS_ERR_NOMEM;
+    }
+    NBLS_CUDA(cudaMemcpyAsync(d, h.data(), (size_t)L * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream));
+    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->fft_tw[L] = d;
+    *out = (const double2*)d;
+    return NBLS_OK;
+}
+
+int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
+                   int max_lag, int32_t* lag, double* cmax) {
+    if (W <= 0) return NBLS_OK;
+    const XfPlan* pl = pick_plan(N, max_lag);
+    if (!pl) {
+        set_error("nbls_xcorr(fft): no transform length for a window of %d samples", N);
+        return NBLS_ERR_UNSUPPORTED;
+    }
+    NBLS_REQUIRE(pl->smem <= ctx->smem_optin, "nbls_xcorr(fft): transform of %d points needs %zu B of shared memory", pl->L,
+                 pl->smem);
+    const int P = C * (C - 1) / 2;
+    NBLS_REQUIRE((int64_t)W * P < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld",
+                 (long long)W * P);
+    const int SP = pl->L / 2 + 1;
+    const double2* tw = nullptr;
+    NBLS_CHECK(twiddles(ctx, pl->L, &tw));
+    // windows per batch: spectra workspace bounded (they are re-read from L2 window by window)
+    const size_t per_win = (size_t)C * SP * sizeof(double2);
+    const size_t budget = (size_t)4 << 30;
+    const int ncp = (C + 1) / 2, npp = (P + 1) / 2;
+    int wb = (int)std::min<int64_t>(W, std::max<int64_t>(1, (int64_t)(budget / per_win)));
+    wb = (int)std::min<int64_t>(wb, ((1LL << 31) - 1) / std::max(npp, ncp));
+    NBLS_CHECK(ensure(ctx, ctx->spec, (size_t)wb * per_win));
+    NBLS_CHECK(ensure(ctx, ctx->energy, (size_t)wb * C * sizeof(double)));
+    NBLS_CHECK(ensure(ctx, ctx->flags, ((size_t)wb * P + 4) * sizeof(int)));
+    NBLS_CUDA(cudaFuncSetAttribute(pl->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
+    NBLS_CUDA(cudaFuncSetAttribute(pl->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
+
+    XfArgs a;
+    memset(&a, 0, sizeof(a));
+    a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first;
+    a.lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
+    a.SP = SP; a.tw = tw;
+    a.spec = (double2*)ctx->spec.p;
+    a.energy = (double*)ctx->energy.p;
+    a.lag = lag; a.cmax = cmax;
+    a.flag_count = (int*)ctx->flags.p;
+    a.flag_list = a.flag_count + 4;
+    for (int w0 = 0; w0 < W; w0 += wb) {
+        a.w0 = w0;
+        a.wn = std::min(wb, W - w0);
+        NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
+        pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        pl->pair<<<(unsigned)(a.wn * npp), pl->threads, pl->smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 2;
+        // near-tied arg-maxima are settled by the time-domain kernel (normally an empty list)
+        NBLS_CHECK(xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
+                                     ctx->sm_count * 2));
+    }
+    return NBLS_OK;
+}
+
+}  // namespace nbls

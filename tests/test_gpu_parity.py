@@ -71,8 +71,9 @@ def test_filter_matches_oracle(eng, name):
             assert np.allclose(out[b][:, :64], g[f"b{b}_filt_head"], rtol=0, atol=1e-12 * float(rms.max()))
 
 
+@pytest.mark.parametrize("method", [_capi.XCORR_DIRECT, _capi.XCORR_FFT], ids=["direct", "fft"])
 @pytest.mark.parametrize("name", sorted(CASES))
-def test_xcorr_lags_bit_exact(eng, name):
+def test_xcorr_lags_bit_exact(eng, name, method):
     g, rec, _, pkw = _case(name)
     fl, wl = g["freqlist"], g["winlen_list"]
     nb = int(g["nbands"])
@@ -81,7 +82,7 @@ def test_xcorr_lags_bit_exact(eng, name):
     n = [int(g[f"b{b}_winlensamp"]) for b in range(nb)]
     hop = [int(g[f"b{b}_sampinc"]) for b in range(nb)]
     cnt = [len(g[f"b{b}_intervals"]) for b in range(nb)]
-    lag, cmax = eng.xcorr(filt, n, hop, cnt, method=_capi.XCORR_DIRECT)
+    lag, cmax = eng.xcorr(filt, n, hop, cnt, method=method)
     row = 0
     for b in range(nb):
         r = slice(row, row + cnt[b])
@@ -157,9 +158,57 @@ def test_ltsva_surface_and_restricted_lag(eng):
     n, hop, starts = orc.window_grid(rec.npts, rec.fs, float(g["winlen_list"][0]), float(g["winover"]))
     pairs, *_ = orc.co_array(g["b0_rij"])
     ref_lag, ref_cmax, *_ = orc.correlate_windows(np.ascontiguousarray(filt.T), starts, n, rec.fs, pairs, None, L)
-    lag, cmax = eng.xcorr(filt[None], [n], [hop], [len(starts)], max_lag=L, method=_capi.XCORR_DIRECT)
-    assert np.array_equal(lag.T, ref_lag)
-    assert np.allclose(cmax.T, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
+    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT):
+        lag, cmax = eng.xcorr(filt[None], [n], [hop], [len(starts)], max_lag=L, method=method)
+        assert np.array_equal(lag.T, ref_lag), method
+        assert np.allclose(cmax.T, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
+
+
+def _oracle_xcorr(x, n, hop, count, fs=100.0, max_lag=None):
+    c = x.shape[0]
+    rij = np.vstack([np.arange(c, dtype=float), np.arange(c, dtype=float) ** 2])
+    pairs, *_ = orc.co_array(rij)
+    starts = np.arange(count) * hop
+    lag, cmax, *_ = orc.correlate_windows(np.ascontiguousarray(x.T), starts, n, fs, pairs, None, max_lag)
+    return lag.T, cmax.T
+
+
+def test_xcorr_fft_ties_and_unequal_amplitudes(eng):
+    """Exact ties (two equal peaks: np.argmax keeps the first) are settled by the time-domain kernel; channels of very
+    different amplitude share one packed transform without losing the weak one's arg-max; dead channel -> NaN."""
+    rng = np.random.default_rng(5)
+    n, hop, count = 700, 350, 6
+    t = n + hop * (count - 1) + 3
+    x = np.zeros((5, t))
+    tt = np.arange(t) % hop               # spikes repeating with the hop: every window sees the same picture
+    x[0] = ((tt == 100) | (tt == 300)).astype(float)   # c_01 has two exactly equal maxima, lags 0 and +200
+    x[1] = (tt == 100).astype(float)
+    x[2] = rng.standard_normal(t) * 1e9   # strong rider
+    x[3] = np.roll(x[2], 7) * 1e-15 + rng.standard_normal(t) * 1e-16   # weak rider, delayed copy
+    x[4] = 0.0                            # dead channel
+    ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
+    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT):
+        lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=method)
+        assert np.array_equal(lag, ref_lag), method
+        assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-12, equal_nan=True), method
+
+
+@pytest.mark.parametrize("n", [128, 255, 384, 700, 1023, 1200, 1537, 2048, 3000, 3100, 4097, 6000, 6144])
+def test_xcorr_fft_every_transform_length(eng, n):
+    """One window length per transform size (512 ... 12288 points), odd channel and pair counts."""
+    rng = np.random.default_rng(n)
+    c, count = 5, 3
+    hop = n // 2
+    t = n + hop * (count - 1) + 5
+    s = rng.standard_normal(t + 64)
+    x = np.stack([s[k * 3:k * 3 + t] + 0.5 * rng.standard_normal(t) for k in range(c)])
+    ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
+    lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=_capi.XCORR_FFT)
+    assert np.array_equal(lag, ref_lag)
+    assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
+    lag2, _ = eng.xcorr(x[None], [n], [hop], [count], max_lag=n // 10, method=_capi.XCORR_FFT)
+    ref2, _ = _oracle_xcorr(x, n, hop, count, max_lag=n // 10)
+    assert np.array_equal(lag2, ref2)
 
 
 def test_errors_mirror_reference(eng):
