@@ -320,24 +320,40 @@ def main():
         return
     j, plan = r["j"], r["plan"]
     peaks, peak_src = measured_peaks()
-    # algorithmic work of this rank's launches; DESIGN.md restates the formulas
+    # algorithmic work of this rank's launches (formulas restated in DESIGN.md §Measurement)
+    from narrow_band_least_squares_b200 import _capi
+    lib = _capi.load()
     B, C, P = plan.nbands, plan.nchan, plan.npairs
     T = plan.npts
-    fma = float(sum(int(plan.win_count[b]) * P * (-(-int(plan.win_len[b]) // 8) * 8.0) ** 2 for b in range(B)))
+    flop, n_fft_bands = 0.0, 0
+    for b in range(B):
+        W, N = int(plan.win_count[b]), int(plan.win_len[b])
+        L = 0
+        if args.method != "direct" and (args.method == "fft" or N >= 128):
+            L = int(lib.nbls_xcorr_fft_length(N, args.max_lag))
+        if L:      # FFT path: ceil(C/2) forward + ceil(P/2) inverse complex FFTs of L points (5 L log2 L each),
+            n_fft_bands += 1       # cross-spectra 2 x 6 flop and arg-max 2 compares per point of the inverse
+            flop += W * (((C + 1) // 2 + (P + 1) // 2) * 5.0 * L * np.log2(L) + ((P + 1) // 2) * L * 16.0)
+        else:      # time-domain path: M^2 multiply-adds per pair, M = N rounded up to 8
+            flop += W * P * 2.0 * (-(-N // 8) * 8.0) ** 2
     x_ms, f_ms = r["stage"]["xcorr"], r["stage"]["filter"]
-    tfl = 2.0 * fma / (x_ms * 1e-3) / 1e12 if x_ms > 0 else None
+    tfl = flop / (x_ms * 1e-3) / 1e12 if x_ms > 0 else None
     filt_bytes = 8.0 * C * T * (1 + 3 * B)
     fgb = filt_bytes / (f_ms * 1e-3) / 1e9 if f_ms > 0 else None
+    kern = ("xf_pair_kernel + xf_spectra_kernel (FP64 FFT cross-correlation)" if n_fft_bands == B else
+            "xcorr_direct_kernel" if n_fft_bands == 0 else "xcorr (FFT and time-domain bands)")
     line = {"metric": "NBLS band-window estimates/sec", "value": r["value"], "unit": "estimates/s",
             "n_gpus": r["world"], "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": config_block(j, r["world"], args, {"estimates_per_step": r["e_total"]}),
             "clocks": r["clocks"], "gpu_launches": int(r["launches"]), "e2e": r["e2e"],
             "stage_ms": r["stage"], "wall_ms_per_step": r["wall_ms"] / args.steps,
-            "roofline": {"kernel": "xcorr (dominant)", "bound": "fp64", "achieved": tfl, "peak": r["fp64_peak"],
+            "roofline": {"kernel": kern, "bound": "fp64", "achieved": tfl, "peak": r["fp64_peak"],
                          "unit": "TFLOP/s", "frac": (tfl / r["fp64_peak"]) if tfl else None, "traffic": None,
-                         "peak_source": "DFMA microbenchmark run in this process (MEASURED_PEAKS.json has no FP64 entry)",
-                         "algorithmic_flop_per_launch_set": 2.0 * fma},
+                         "peak_source": "DFMA microbenchmark run in this process, 2 flop per FMA (MEASURED_PEAKS.json has no "
+                                        "FP64 entry); FFT butterflies are mostly unfused adds, so 0.5 is the ceiling of this "
+                                        "fraction - see DESIGN.md and profiles/ for the FP64-pipe utilisation from ncu",
+                         "algorithmic_flop_per_step": flop},
             "roofline_filter": {"kernel": "biquad_chunk_kernel x6 + carry x2", "bound": "hbm", "achieved": fgb,
                                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (fgb / peaks["hbm_gbs"]) if fgb else None,
                                 "peak_source": peak_src, "algorithmic_bytes": filt_bytes, "traffic": None}}

@@ -96,6 +96,11 @@ typedef struct nbls_window_desc {
 int nbls_xcorr(nbls_ctx* ctx, const nbls_window_desc* win, const double* y_dev, int32_t nchan,
                int64_t ldy, int64_t ystride_band, int32_t* lag_dev, double* cmax_dev);
 
+/* Transform length the FFT path uses for windows of `win_len` samples and lag bound `max_lag` (as in
+ * nbls_window_desc); 0 if the FFT path does not cover that window length (NBLS_XCORR_AUTO then runs the
+ * time-domain kernel).  Pure host arithmetic, needs no context. */
+int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag);
+
 /* ---- K3: per-window statistics and slowness solve ---------------------------------- */
 typedef struct nbls_solve_desc {
     int32_t nchan;            /* C */

@@ -355,6 +355,8 @@ int nbls_xcorr(nbls_ctx* ctx, const nbls_window_desc* win, const double* y_dev, 
     return xcorr_impl(ctx, win, y_dev, nchan, ldy, ystride_band, lag_dev, cmax_dev);
 }
 
+int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag) { return xcorr_fft_length(win_len, max_lag); }
+
 int nbls_solve(nbls_ctx* ctx, const nbls_solve_desc* sol, int64_t nwin, const int32_t* lag_dev, const double* cmax_dev,
                const nbls_outputs* out_dev) {
     NBLS_REQUIRE(ctx, "nbls_solve: null context");

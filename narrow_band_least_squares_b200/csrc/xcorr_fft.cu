@@ -97,21 +97,22 @@ __device__ __forceinline__ void pass2(double2* sm, const double2* tw, int tid) {
         double2 z[S::R2];
 #pragma unroll
         for (int k = 0; k < S::R2; ++k) z[k] = base[S::ROW * k];
+        // twiddles w_L^{R1 f1 n2} = W1^n2: one table entry, the powers by a product tree
+        double2 Wp[S::R2];
+        Wp[0] = make_double2(1.0, 0.0);
+        Wp[1] = ldg2(tw + S::R1 * f1);
         Dft<S::R2>::run(z);
-        const double2* t = tw + S::R1 * f1;          // w_L^{R1 f1 n2}
+        powers<S::R2>(Wp);
 #pragma unroll
-        for (int n2 = 0; n2 < S::R2; ++n2) {
-            const double2 v = n2 == 0 ? z[0] : cmul(z[n2], ldg2(t + (S::R1 * f1) * (n2 - 1)));
-            base[S::ROW * n2] = v;
-        }
+        for (int n2 = 0; n2 < S::R2; ++n2) base[S::ROW * n2] = n2 == 0 ? z[0] : cmul(z[n2], Wp[n2]);
     }
 }
 
 // ---- spectra kernel -------------------------------------------------------------------------
 // grid = wn * ceil(C/2); CTA (w, cp) transforms channels a = 2cp and b = 2cp+1 of window w.
 // Forward DFT through the inverse machinery: Y = IDFT(conj z)  =>  Z = conj(Y).
-template <class S, int T>
-__global__ void __launch_bounds__(T) xf_spectra_kernel(XfArgs g) {
+template <class S, int T, int MINB>
+__global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     extern __shared__ __align__(16) double2 xf_smem[];
     double2* sm = xf_smem;
     __shared__ double red[2][T / 32];
@@ -192,8 +193,8 @@ struct Top {       // best and second-best value seen, lag of the best
     double b1, b2;
     int l1;
 };
-__device__ __forceinline__ void top_push(Top& t, double v, int lag) {
-    const bool p1 = v > t.b1, p2 = v > t.b2;
+__device__ __forceinline__ void top_push(Top& t, double v, int lag, bool ok) {
+    const bool p1 = ok & (v > t.b1), p2 = ok & (v > t.b2);     // bitwise: no short-circuit branches
     t.b2 = p1 ? t.b1 : (p2 ? v : t.b2);
     t.b1 = p1 ? v : t.b1;
     t.l1 = p1 ? lag : t.l1;
@@ -215,7 +216,8 @@ __device__ __forceinline__ void pair_channels(int p, int C, int& ci, int& cj) {
 }
 
 // pass-1 stores of the partner butterflies f0 = t (A) and M1 - t (B); W[n] = w_L^{t n}, so B's twiddle
-// is w_L^{(M1-t) n} = e^{2 pi i n/R1} conj(W[n])
+// is w_L^{(M1-t) n} = e^{2 pi i n/R1} conj(W[n]); the constant factor e^{2 pi i n/R1} was applied for free
+// by feeding B's inputs to the butterfly rotated by one position (DFT shift theorem)
 template <class S, int N1>
 __device__ __forceinline__ void store_pair(const double2 (&zA)[S::R1], const double2 (&zB)[S::R1],
                                            const double2 (&W)[S::R1], int t, double2* sm) {
@@ -225,7 +227,7 @@ __device__ __forceinline__ void store_pair(const double2 (&zA)[S::R1], const dou
             sm[S::pad(S::M1 - t)] = zB[0];
         } else {
             sm[S::pad(N1 * S::M1 + t)] = cmul(zA[N1], W[N1]);
-            sm[S::pad(N1 * S::M1 + S::M1 - t)] = cmul(zB[N1], mul_root<N1, S::R1>(cconj(W[N1])));
+            sm[S::pad(N1 * S::M1 + S::M1 - t)] = cmulc(zB[N1], W[N1]);
         }
         store_pair<S, N1 + 1>(zA, zB, W, t, sm);
     }
@@ -280,18 +282,28 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             continue;
         }
         double2 zA[R1], zB[R1];
+        // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd)
+        constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
+        {   // every load of the task is issued before the first use: one L2 round trip per task
+            double2 vi0[R1], vj0[R1], vi1[R1], vj1[R1];
 #pragma unroll
-        for (int k = 0; k < R1; ++k) {
-            // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd)
-            constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
-            const bool direct = k < HALF;
-            const int f = t + M1 * k;
-            double2 a, b;
-            cross(direct ? f : L - f, a, b);
-            const double2 zg = make_double2(a.x - b.y, a.y + b.x);     // Z[g]
-            const double2 zm = make_double2(a.x + b.y, b.x - a.y);     // Z[L-g]
-            zA[k] = direct ? zg : zm;
-            zB[R1 - 1 - k] = direct ? zm : zg;
+            for (int k = 0; k < R1; ++k) {
+                const int f = t + M1 * k;
+                const int gi = k < HALF ? f : L - f;
+                vi0[k] = ldg2(Xi0 + gi);
+                vj0[k] = ldg2(Xj0 + gi);
+                vj1[k] = has1 ? ldg2(Xj1 + gi) : make_double2(0.0, 0.0);
+                vi1[k] = same_i ? vi0[k] : ldg2(Xi1 + gi);
+            }
+#pragma unroll
+            for (int k = 0; k < R1; ++k) {
+                const bool direct = k < HALF;
+                const double2 a = cmulc(vi0[k], vj0[k]), b = cmulc(vi1[k], vj1[k]);
+                const double2 zg = make_double2(a.x - b.y, a.y + b.x);     // Z[g]
+                const double2 zm = make_double2(a.x + b.y, b.x - a.y);     // Z[L-g]
+                zA[k] = direct ? zg : zm;
+                zB[(R1 - k) % R1] = direct ? zm : zg;      // slot R1-1-k, rotated by one (see store_pair)
+            }
         }
         Dft<R1>::run(zA);
         Dft<R1>::run(zB);
@@ -303,12 +315,21 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     }
     __syncthreads();
     pass2<S, T>(sm, g.tw, tid);
-    __syncthreads();
+    // with R2 = R3 = 32 and one warp per n1, a warp's pass-3 rows are exactly the rows it wrote in pass 2
+    if constexpr (S::R2 == 32 && S::R3 == 32 && T == 32 * R1) __syncwarp();
+    else __syncthreads();
 
     // ---- pass 3 + arg-max straight from registers ----
-    Top tr = {-CUDART_INF, -CUDART_INF, INT_MAX}, ti = {-CUDART_INF, -CUDART_INF, INT_MAX};
+    constexpr int NCH = 4;     // independent arg-max chains per component (the update is a serial dependency)
+    Top accr = {-CUDART_INF, -CUDART_INF, INT_MAX}, acci = {-CUDART_INF, -CUDART_INF, INT_MAX};
     const int lag_max = g.lag_max;
     for (int u = tid; u < L / S::R3; u += T) {
+        Top tr[NCH], ti[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            tr[c].b1 = tr[c].b2 = ti[c].b1 = ti[c].b2 = -CUDART_INF;
+            tr[c].l1 = ti[c].l1 = INT_MAX;
+        }
         const double2* base = sm + S::ROW * u;
         double2 z[S::R3];
 #pragma unroll
@@ -316,25 +337,36 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         Dft<S::R3>::run(z);
         const int n1 = u / S::R2, n2 = u - n1 * S::R2;
         const int nb = n1 + R1 * n2;
+        // circular index n = nb + R1 R2 n3 stands for lag n (n <= lag_max) or n - L (n >= L - lag_max): the wanted
+        // n3 are [0, n3a] and [n3b, R3); the chains record n3, the lag is rebuilt afterwards
+        constexpr int STEP = R1 * S::R2;
+        const int n3a = lag_max >= nb ? (lag_max - nb) / STEP : -1;
+        const int n3b = (max(L - lag_max - nb, 0) + STEP - 1) / STEP;
 #pragma unroll
         for (int n3 = 0; n3 < S::R3; ++n3) {
-            const int n = nb + R1 * S::R2 * n3;            // circular index: lag n, or n - L
-            const int lag = n <= lag_max ? n : n - L;
-            const bool ok = (n <= lag_max) || (n >= L - lag_max);
-            top_push(tr, ok ? z[n3].x : -CUDART_INF, lag);
-            top_push(ti, ok ? z[n3].y : -CUDART_INF, lag);
+            const bool ok = (n3 <= n3a) | (n3 >= n3b);
+            top_push(tr[n3 % NCH], z[n3].x, n3, ok);
+            top_push(ti[n3 % NCH], z[n3].y, n3, ok);
+        }
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {      // n3 -> lag, then fold the chain into the thread's result
+            const int nr = nb + STEP * tr[c].l1, ni = nb + STEP * ti[c].l1;
+            const int lr = tr[c].l1 == INT_MAX ? INT_MAX : (nr <= lag_max ? nr : nr - L);
+            const int li = ti[c].l1 == INT_MAX ? INT_MAX : (ni <= lag_max ? ni : ni - L);
+            top_merge(accr, tr[c].b1, tr[c].b2, lr);
+            top_merge(acci, ti[c].b1, ti[c].b2, li);
         }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        top_merge(tr, __shfl_xor_sync(0xffffffffu, tr.b1, o), __shfl_xor_sync(0xffffffffu, tr.b2, o),
-                  __shfl_xor_sync(0xffffffffu, tr.l1, o));
-        top_merge(ti, __shfl_xor_sync(0xffffffffu, ti.b1, o), __shfl_xor_sync(0xffffffffu, ti.b2, o),
-                  __shfl_xor_sync(0xffffffffu, ti.l1, o));
+        top_merge(accr, __shfl_xor_sync(0xffffffffu, accr.b1, o), __shfl_xor_sync(0xffffffffu, accr.b2, o),
+                  __shfl_xor_sync(0xffffffffu, accr.l1, o));
+        top_merge(acci, __shfl_xor_sync(0xffffffffu, acci.b1, o), __shfl_xor_sync(0xffffffffu, acci.b2, o),
+                  __shfl_xor_sync(0xffffffffu, acci.l1, o));
     }
     if (lane == 0) {
-        rb1[0][warp] = tr.b1; rb2[0][warp] = tr.b2; rl1[0][warp] = tr.l1;
-        rb1[1][warp] = ti.b1; rb2[1][warp] = ti.b2; rl1[1][warp] = ti.l1;
+        rb1[0][warp] = accr.b1; rb2[0][warp] = accr.b2; rl1[0][warp] = accr.l1;
+        rb1[1][warp] = acci.b1; rb2[1][warp] = acci.b2; rl1[1][warp] = acci.l1;
     }
     __syncthreads();
     if (tid < 2 && (tid == 0 || has1)) {
@@ -376,7 +408,7 @@ static XfPlan make_plan() {
     p.L = S::L;
     p.threads = T;
     p.smem = (size_t)S::SMEM_ELEMS * sizeof(double2);
-    p.spectra = xf_spectra_kernel<S, T>;
+    p.spectra = xf_spectra_kernel<S, T, MINB>;
     p.pair = xf_pair_kernel<S, T, MINB>;
     return p;
 }
