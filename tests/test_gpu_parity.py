@@ -221,3 +221,38 @@ def test_errors_mirror_reference(eng):
         ltsva((x, 40.0), None, None, 10.0, 0.5, 0.75, rij=np.array([[0.0, 1.0, 0.3], [0.0, 0.5, 0.9]]), engine=eng)
     with pytest.raises(RuntimeError):     # collinear array: rank-deficient co-array
         ltsva((x, 40.0), None, None, 10.0, 0.5, rij=np.array([[0.0, 1.0, 2.0], [0.0, 1.0, 2.0]]), engine=eng)
+
+
+@pytest.mark.parametrize("alpha", [1.0, 0.75])
+def test_time_sharded_run_equals_unsharded(eng, alpha):
+    """Three logical time shards (filter halos, global taper index) on one GPU reproduce the unsharded lags, LTS flags
+    and estimates: the multi-GPU path without a cluster."""
+    from narrow_band_least_squares_b200.engine import Plan, Results, window_grid
+    from narrow_band_least_squares_b200.sharding import Shard, filter_halo, merge_band_major
+    rec = plane_wave_record(seed=21, nchans=6, npts=240000, fs=100.0, aperture_km=0.5, flip_channel=3)
+    fl = orc.get_freqlist_log(0.5, 5.0, 3)
+    sos = np.stack([orc.design_sos("butter", fl[b], fl[b + 1], rec.fs, 2) for b in range(3)])
+    wl = [40.0, 30.0, 20.0]
+    grids = [window_grid(rec.npts, rec.fs, w, 0.5) for w in wl]
+    n = [g[0] for g in grids]; hop = [g[1] for g in grids]; cnt = [g[2] for g in grids]
+    whole = Plan(rec.nchans, rec.npts, rec.fs, sos, True, n, hop, cnt, rec.rij, alpha=alpha)
+    ref = eng.run(whole, rec.data, Results(whole, pinned=False))
+    halo = filter_halo(sos)
+    parts, counts = {k: [] for k in ("lag", "vel", "baz", "mdccm", "sigma_tau", "weights")}, []
+    world = 3
+    for r in range(world):
+        sh = Shard(rec.npts, n, hop, cnt, r, world, halo)
+        plan = sh.plan(rec.nchans, rec.fs, sos, True, n, hop, rec.rij, alpha=alpha)
+        res = eng.run(plan, rec.data[:, sh.seg_lo:sh.seg_hi], Results(plan, pinned=False))
+        counts.append(plan.win_count)
+        for k in parts:
+            a = getattr(res, k)
+            if a is not None:
+                parts[k].append(a[:plan.nwin])
+    assert np.array_equal(merge_band_major(parts["lag"], counts), ref.lag), "sharded lags differ"
+    if alpha != 1.0:
+        assert np.array_equal(merge_band_major(parts["weights"], counts), ref.weights), "sharded LTS flags differ"
+    for k in ("vel", "sigma_tau", "mdccm"):
+        assert np.allclose(merge_band_major(parts[k], counts), getattr(ref, k), rtol=1e-9, atol=1e-12, equal_nan=True), k
+    d = np.abs(((merge_band_major(parts["baz"], counts) - ref.baz + 180.0) % 360.0) - 180.0)
+    assert np.nanmax(d, initial=0.0) < 1e-6

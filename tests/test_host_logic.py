@@ -1,0 +1,206 @@
+"""CPU tests (no GPU): the C-ABI library loads and exports every symbol include/nbls.h declares, and the host-side
+logic (window grid, co-array, LTS tables, result assembly, time-segment sharding) follows the reference."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from narrow_band_least_squares_b200 import _capi, helpers, lts_tables, sharding
+from narrow_band_least_squares_b200.engine import window_grid
+from narrow_band_least_squares_b200.geometry import CoArray, get_rij
+from narrow_band_least_squares_b200.ltsva import build_stdict
+from narrow_band_least_squares_b200.narrow_band_least_squares import reference_vector_len
+from oracle import nbls_oracle as orc
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def test_capi_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "nbls.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(nbls_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = _capi.load()                      # raises if the library was not built
+    for name in sorted(declared):
+        assert hasattr(lib, name), f"{name} is declared in nbls.h but not exported by libnbls.so"
+    assert declared == set(_capi.EXPORTS), "ctypes prototypes and nbls.h disagree"
+    assert lib.nbls_version() >= 100
+
+
+def test_no_cuda_device_fails_loudly():
+    import ctypes as C
+    lib = _capi.load()
+    n = C.c_int32(-1)
+    assert lib.nbls_device_count(C.byref(n)) == 0
+    if n.value == 0:                        # the build container: no CPU fallback may exist
+        ctx = C.c_void_p()
+        assert lib.nbls_create(C.byref(ctx), 0) != 0
+        assert b"no CPU fallback" in lib.nbls_last_error()
+        from narrow_band_least_squares_b200.engine import Engine
+        with pytest.raises(_capi.NBLSError):
+            Engine(0)
+
+
+def test_fft_length_table():
+    lib = _capi.load()
+    assert lib.nbls_xcorr_fft_length(3000, -1) == 6144        # N + (N-1) = 5999 -> 6 * 1024
+    assert lib.nbls_xcorr_fft_length(6000, -1) == 12288
+    assert lib.nbls_xcorr_fft_length(1200, -1) == 3072
+    assert lib.nbls_xcorr_fft_length(3000, 200) == 4096       # restricted lag: N + 200 points suffice
+    assert lib.nbls_xcorr_fft_length(6145, -1) == 0           # beyond one SM's shared memory: time-domain kernel
+    assert lib.nbls_xcorr_fft_length(0, -1) == 0
+
+
+@pytest.mark.parametrize("npts,fs,wl,ov", [(144000, 40.0, 30.0, 0.5), (8640000, 100.0, 30.0, 0.5), (6000, 50.0, 20.0, 0.75),
+                                            (3000, 100.0, 30.0, 0.5), (2999, 100.0, 30.0, 0.5)])
+def test_window_grid_matches_databin(npts, fs, wl, ov):
+    n, hop, w = window_grid(npts, fs, wl, ov)
+    n2, hop2, starts = orc.window_grid(npts, fs, wl, ov)      # lts_data_class.py:58-64
+    assert (n, hop, w) == (n2, hop2, len(starts))
+    if (npts, fs, wl) == (144000, 40.0, 30.0):
+        assert w == 238 and reference_vector_len(npts, fs, [wl], ov) == 239
+    if (npts, fs, wl) == (8640000, 100.0, 30.0):
+        assert w == 5758
+
+
+def test_helpers_follow_reference_lists():
+    fl, nb, _ = helpers.get_freqlist(0.5, 5.0, "log", 8)
+    assert nb == 8 and np.allclose(fl, orc.get_freqlist_log(0.5, 5.0, 8))
+    assert helpers.get_winlenlist("constant", 4, 30, 60, 30) == [30, 30, 30, 30]
+    wl = helpers.get_winlenlist("adaptive", 20, 30, 60, 30)
+    assert len(wl) == 20 and wl[0] == 60 and wl[-1] == 30
+    sos = helpers.design_sos("butter", 0.5, 0.8, 100.0, 2)
+    assert np.array_equal(sos, orc.design_sos("butter", 0.5, 0.8, 100.0, 2))
+    wlen, up, down = helpers.taper_ramps(144000, 0.01)
+    wlen2, up2, down2 = orc.taper_weights(144000, 0.01)
+    assert wlen == wlen2 == 1440 and np.array_equal(up, up2) and np.array_equal(down, down2)
+
+
+def test_coarray_and_lts_tables_match_golden():
+    g = np.load(os.path.join(GOLD, "tables.npz"))
+    for p in (6, 10, 15, 28, 66, 300):
+        assert np.array_equal(lts_tables.subset_stream(p, 520), g[f"randset_{p}"])
+    for p, alpha, h, raw, rew1 in g["factors"]:
+        hh, r, w1, tab = lts_tables.lts_constants(int(p), float(alpha))
+        assert hh == int(h) and r == raw and w1 == rew1
+        assert np.array_equal(tab[1:int(p)], g[f"rewcons_{int(p)}"][1:int(p)], equal_nan=True)
+    rng = np.random.default_rng(3)
+    rij = rng.standard_normal((2, 7))
+    co = CoArray(rij)
+    pairs, xij, mad, xstd = orc.co_array(rij)
+    assert np.array_equal(co.idx, pairs) and np.array_equal(co.xij, xij)
+    assert np.array_equal(co.xij_mad, mad) and np.array_equal(co.xij_standardized, xstd)
+    with pytest.raises(RuntimeError):
+        CoArray(np.array([[0.0, 1.0, 2.0], [0.0, 1.0, 2.0]])).check_rank()
+
+
+def test_stdict_assembly_matches_reference_rule():
+    w = np.ones((6, 3), dtype=np.uint8)
+    w[1, 0] = 0
+    w[:, 2] = 0                                   # skipped window: every pair flagged
+    t = np.array([1.0, 2.0, 3.0])
+    idx = orc.co_array(np.random.default_rng(0).standard_normal((2, 4)))[0]
+    sd = build_stdict(w, t, np.asarray(idx), 4)
+    ref = orc.build_stdict(w, t, idx, 4)
+    assert list(sd) == list(ref) and sd["size"] == 4
+    for k in sd:
+        assert np.array_equal(sd[k], ref[k])
+
+
+def test_vincenty_against_oracle_stub():
+    lat = [64.0, 64.001, 63.9995, 64.0007]
+    lon = [-147.0, -147.002, -146.9991, -147.0012]
+    rij = get_rij(lat, lon)
+    assert rij.shape == (2, 4) and np.allclose(rij.mean(axis=1), 0.0, atol=1e-12)
+    d01 = np.hypot(*(rij[:, 0] - rij[:, 1]))
+    assert 0.12 < d01 < 0.16                      # ~111 m north, ~97 m west
+
+
+# ---- time-segment sharding --------------------------------------------------------------------
+def _bands():
+    fs = 100.0
+    fl = orc.get_freqlist_log(0.5, 5.0, 4)
+    sos = [orc.design_sos("butter", fl[b], fl[b + 1], fs, 2) for b in range(4)]
+    return fs, fl, sos
+
+
+def test_shards_partition_windows_and_keep_halos():
+    fs, fl, sos = _bands()
+    npts = 600000
+    grids = [window_grid(npts, fs, wl, 0.5) for wl in (60.0, 50.0, 40.0, 30.0)]
+    n = [g[0] for g in grids]; hop = [g[1] for g in grids]; cnt = [g[2] for g in grids]
+    halo = sharding.filter_halo(sos)
+    assert halo == max(int(np.ceil(80 * np.log(2) / -np.log(sharding.pole_radius(s)))) for s in sos)
+    for world in (1, 2, 3, 8):
+        shards = [sharding.Shard(npts, n, hop, cnt, r, world, halo) for r in range(world)]
+        for b in range(4):
+            lo = [int(s.w_lo[b]) for s in shards]; hi = [int(s.w_hi[b]) for s in shards]
+            assert lo[0] == 0 and hi[-1] == cnt[b]
+            assert all(hi[r] == lo[r + 1] for r in range(world - 1))          # disjoint, complete, ordered
+        for s in shards:
+            assert s.seg_lo % 16 == 0 and 0 <= s.seg_lo < s.seg_hi <= npts
+            for b in range(4):
+                if s.win_count[b]:
+                    first = int(s.win_first[b]) + s.seg_lo
+                    last_end = first + (int(s.win_count[b]) - 1) * hop[b] + n[b]
+                    assert first == int(s.w_lo[b]) * hop[b]
+                    assert first - s.seg_lo >= (halo if s.rank > 0 else 0) - 15
+                    assert s.seg_hi - last_end >= (halo if s.rank < world - 1 else 0) or s.seg_hi == npts
+        assert shards[0].seg_lo == 0 and shards[-1].seg_hi == npts
+
+
+def test_halo_makes_segment_filter_equal_whole_record_filter():
+    """The oracle filter on a halo-padded segment agrees with the whole-record filter inside the owned windows
+    to below FP64 rounding, which is what makes sharded lags equal unsharded ones."""
+    fs, fl, sos = _bands()
+    rng = np.random.default_rng(11)
+    npts = 400000
+    x = rng.standard_normal((2, npts))
+    halo = sharding.filter_halo(sos)
+    whole = [orc.filter_record(x, fs, "butter", fl[b], fl[b + 1], 2, taper=None)[0] for b in range(4)]
+    grids = [window_grid(npts, fs, 30.0, 0.5)] * 4
+    sh = sharding.Shard(npts, [g[0] for g in grids], [g[1] for g in grids], [g[2] for g in grids], 1, 3, halo)
+    seg = x[:, sh.seg_lo:sh.seg_hi]
+    for b in range(4):
+        part = orc.filter_record(seg, fs, "butter", fl[b], fl[b + 1], 2, taper=None)[0]
+        a = int(sh.win_first[b]); z = a + (int(sh.win_count[b]) - 1) * grids[b][1] + grids[b][0]
+        ref = whole[b][:, sh.seg_lo + a:sh.seg_lo + z]
+        assert np.max(np.abs(part[:, a:z] - ref)) <= 1e-13 * np.max(np.abs(ref))
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        counts = [3 + rank, 2, 0 if rank == 0 else 4]                 # windows per band on this rank
+        e = sum(counts)
+        base = 1000 * rank
+        local = {"vel": base + np.arange(e, dtype=np.float64), "lag": (base + np.arange(e * 5, dtype=np.int32)).reshape(e, 5)}
+        out = sharding.gather_results(local, counts)
+        q.put((rank, {k: v.tolist() for k, v in out.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gather_results_world2_gloo():
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # global band-major order: band 0 of rank 0, band 0 of rank 1, band 1 of rank 0, ...
+    r0 = np.arange(5, dtype=float); r1 = 1000 + np.arange(10, dtype=float)
+    exp = np.concatenate([r0[0:3], r1[0:4], r0[3:5], r1[4:6], r1[6:10]])
+    for rank in (0, 1):
+        assert np.array_equal(np.array(got[rank]["vel"]), exp)
+        assert np.array(got[rank]["lag"]).shape == (15, 5)
