@@ -28,12 +28,15 @@
 
 namespace nbls {
 
-constexpr int FT_TILE = 16;    // samples per chunk per step (one 128-B line)
-constexpr int FT_ROW = 18;     // padded row stride in doubles: 144 B keeps 16-B alignment and
+constexpr int FT_TILE = 16;    // samples per chunk per step (one 128-B line; 32 = 256 B was measured: no gain)
+constexpr int FT_ROW = FT_TILE + 2;   // padded row stride in doubles: (8 TILE + 16) B keeps 16-B alignment and
                                // makes lane r's LDS.128 hit banks 4r..4r+3 (conflict-free)
 constexpr int FT_STAGES = 3;   // cp.async ring depth
 constexpr int FT_WARPS = 4;    // bands per block
 constexpr int FT_TILE_DOUBLES = 32 * FT_ROW;
+constexpr int FT_SEGS = FT_TILE / 2;          // 16-byte segments per tile row
+constexpr int FT_ROWS_PER_REQ = 32 / FT_SEGS; // rows covered by one warp-wide request
+constexpr int FT_REQS = 32 / FT_ROWS_PER_REQ; // requests per tile
 
 struct FilterArgs {
     const double* in;
@@ -63,19 +66,14 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
 }
 
-template <int S, bool REV>
-__global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs a) {
-    extern __shared__ __align__(16) double smem[];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int band = blockIdx.x * FT_WARPS + warp;
-    if (band >= a.B) return;   // warps are independent: only warp-level synchronisation below
-    const int chan = blockIdx.z;
-    const int64_t chunk0 = (int64_t)blockIdx.y * 32;
-    double* ring = smem + warp * (FT_STAGES * FT_TILE_DOUBLES);
+// One warp, 32 consecutive chunks of one (band, channel).  EDGE = false is the interior fast path: every chunk of
+// the warp is whole and no sample lies in the taper zones, so loads and stores carry no bounds or taper logic.
+template <int S, bool REV, bool EDGE, bool STATE_ONLY>
+__device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, int band, int chan, int64_t chunk0,
+                                            int lane) {
     const int ntiles = a.L / FT_TILE;
     int first = 0;
     if (a.proc_tiles) first = ntiles - min(ntiles, a.proc_tiles[band]);
-
     const double* in = a.in + (int64_t)band * a.in_band + (int64_t)chan * a.in_row;
     double* out = a.out ? a.out + (int64_t)band * a.out_band + (int64_t)chan * a.out_row : nullptr;
 
@@ -87,30 +85,37 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
         z0[s] = 0.0; z1[s] = 0.0;
     }
     const int64_t mychunk = chunk0 + lane;
-    const bool valid = mychunk < a.nchunks;
+    const bool valid = !EDGE || mychunk < a.nchunks;
     const int64_t sidx = (((int64_t)band * a.C + chan) * a.nchunks + mychunk) * (2 * S);
     if (a.state_in && valid) {
 #pragma unroll
         for (int s = 0; s < S; ++s) { z0[s] = a.state_in[sidx + 2 * s]; z1[s] = a.state_in[sidx + 2 * s + 1]; }
     }
 
-    // the copy this lane performs for each of its 8 slots of a tile: row = slot*4 + lane/8
-    const int seg = lane & 7;
+    // the copy this lane performs for each of its slots of a tile: row = slot*ROWS_PER_REQ + lane/SEGS
+    const int seg = lane % FT_SEGS, row0 = lane / FT_SEGS;
+    const int64_t lane_t0 = (chunk0 + row0) * a.L + seg * 2;      // sample index of slot 0, tile offset 0
+    const int64_t slot_stride = (int64_t)FT_ROWS_PER_REQ * a.L;   // samples between consecutive slots
+    double* const lane_dst = ring + row0 * FT_ROW + seg * 2;
     auto tile_off = [&](int i) -> int { return FT_TILE * (REV ? (ntiles - 1 - i) : i); };
     auto issue = [&](int i, int stage) {
-        double* dst0 = ring + stage * FT_TILE_DOUBLES;
-        const int off = tile_off(i) + seg * 2;
+        double* dst = lane_dst + stage * FT_TILE_DOUBLES;
+        const int64_t t0 = lane_t0 + tile_off(i);
+        const double* src = in + t0;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int row = q * 4 + (lane >> 3);
-            const int64_t k = chunk0 + row;
-            const int64_t t = k * a.L + off;
-            int bytes = 0;
-            if (k < a.nchunks) {
-                const int64_t left = a.T - t;
-                bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
+        for (int q = 0; q < FT_REQS; ++q) {
+            if constexpr (!EDGE) {
+                cp_async16(dst + q * FT_ROWS_PER_REQ * FT_ROW, src + q * slot_stride, 16);
+            } else {
+                const int64_t k = chunk0 + row0 + q * FT_ROWS_PER_REQ;
+                const int64_t t = t0 + q * slot_stride;
+                int bytes = 0;
+                if (k < a.nchunks) {
+                    const int64_t left = a.T - t;
+                    bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
+                }
+                cp_async16(dst + q * FT_ROWS_PER_REQ * FT_ROW, bytes ? (const void*)(in + t) : (const void*)in, bytes);
             }
-            cp_async16(dst0 + row * FT_ROW + seg * 2, bytes ? (const void*)(in + t) : (const void*)in, bytes);
         }
     };
 
@@ -144,36 +149,49 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
             double x = v[j];
 #pragma unroll
             for (int s = 0; s < S; ++s) {
-                // scipy _sosfilt order, unfused
-                const double y = __dadd_rn(__dmul_rn(b0[s], x), z0[s]);
-                z0[s] = __dadd_rn(__dsub_rn(__dmul_rn(b1[s], x), __dmul_rn(a1[s], y)), z1[s]);
-                z1[s] = __dsub_rn(__dmul_rn(b2[s], x), __dmul_rn(a2[s], y));
-                x = y;
+                if constexpr (STATE_ONLY) {
+                    // phase 1 only feeds the chunk-state scan, whose reassociation already differs from the
+                    // sequential order by rounding: fused multiply-adds halve its FP64 instruction count
+                    const double y = fma(b0[s], x, z0[s]);
+                    z0[s] = fma(b1[s], x, fma(-a1[s], y, z1[s]));
+                    z1[s] = fma(b2[s], x, -(a2[s] * y));
+                    x = y;
+                } else {
+                    // scipy _sosfilt order, unfused
+                    const double y = __dadd_rn(__dmul_rn(b0[s], x), z0[s]);
+                    z0[s] = __dadd_rn(__dsub_rn(__dmul_rn(b1[s], x), __dmul_rn(a1[s], y)), z1[s]);
+                    z1[s] = __dsub_rn(__dmul_rn(b2[s], x), __dmul_rn(a2[s], y));
+                    x = y;
+                }
             }
             v[j] = x;
         }
-        if (out) {
+        if (!STATE_ONLY && out) {
 #pragma unroll
             for (int q = 0; q < FT_TILE / 2; ++q) row[q] = make_double2(v[2 * q], v[2 * q + 1]);
             __syncwarp();
-            const int off = tile_off(i) + seg * 2;
+            const int64_t t0 = lane_t0 + tile_off(i);
+            const double* srow = tile + row0 * FT_ROW + seg * 2;
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int r = q * 4 + (lane >> 3);
-                const int64_t k = chunk0 + r;
-                const int64_t t = k * a.L + off;
-                if (k < a.nchunks && t < a.T) {
-                    double2 d = *reinterpret_cast<const double2*>(tile + r * FT_ROW + seg * 2);
-                    if (a.taper_len > 0) {
-                        const int64_t g = a.g0 + t;
-                        const int64_t dn = a.G - a.taper_len;
-                        if (g < a.taper_len) d.x = __dmul_rn(d.x, a.taper_up[g]);
-                        if (g + 1 < a.taper_len) d.y = __dmul_rn(d.y, a.taper_up[g + 1]);
-                        if (g >= dn && g < a.G) d.x = __dmul_rn(d.x, a.taper_down[g - dn]);
-                        if (g + 1 >= dn && g + 1 < a.G) d.y = __dmul_rn(d.y, a.taper_down[g + 1 - dn]);
+            for (int q = 0; q < FT_REQS; ++q) {
+                double2 d = *reinterpret_cast<const double2*>(srow + q * FT_ROWS_PER_REQ * FT_ROW);
+                const int64_t t = t0 + q * slot_stride;
+                if constexpr (!EDGE) {
+                    *reinterpret_cast<double2*>(out + t) = d;
+                } else {
+                    const int64_t k = chunk0 + row0 + q * FT_ROWS_PER_REQ;
+                    if (k < a.nchunks && t < a.T) {
+                        if (a.taper_len > 0) {
+                            const int64_t g = a.g0 + t;
+                            const int64_t dn = a.G - a.taper_len;
+                            if (g < a.taper_len) d.x = __dmul_rn(d.x, a.taper_up[g]);
+                            if (g + 1 < a.taper_len) d.y = __dmul_rn(d.y, a.taper_up[g + 1]);
+                            if (g >= dn && g < a.G) d.x = __dmul_rn(d.x, a.taper_down[g - dn]);
+                            if (g + 1 >= dn && g + 1 < a.G) d.y = __dmul_rn(d.y, a.taper_down[g + 1 - dn]);
+                        }
+                        if (t + 1 < a.T) *reinterpret_cast<double2*>(out + t) = d;
+                        else out[t] = d.x;
                     }
-                    if (t + 1 < a.T) *reinterpret_cast<double2*>(out + t) = d;
-                    else out[t] = d.x;
                 }
             }
         }
@@ -184,6 +202,30 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
     if (a.state_out && valid) {
 #pragma unroll
         for (int s = 0; s < S; ++s) { a.state_out[sidx + 2 * s] = z0[s]; a.state_out[sidx + 2 * s + 1] = z1[s]; }
+    }
+}
+
+template <int S, bool REV>
+__global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs a) {
+    extern __shared__ __align__(16) double smem[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int band = blockIdx.x * FT_WARPS + warp;
+    if (band >= a.B) return;   // warps are independent: only warp-level synchronisation below
+    const int chan = blockIdx.z;
+    const int64_t chunk0 = (int64_t)blockIdx.y * 32;
+    double* ring = smem + warp * (FT_STAGES * FT_TILE_DOUBLES);
+    // interior warp: its 32 chunks are whole (none is the record's ragged last chunk) and, when a taper is applied by
+    // this launch, none of its samples lies in the first / last taper_len samples of the global record
+    const int64_t s_lo = chunk0 * a.L, s_hi = (chunk0 + 32) * a.L;          // local sample range [s_lo, s_hi)
+    bool edge = s_hi > a.T;
+    if (a.out && a.taper_len > 0)
+        edge = edge || (a.g0 + s_lo < a.taper_len) || (a.g0 + s_hi > a.G - a.taper_len);
+    if (!a.out) {     // phase 1: chunk end states only
+        if (edge) biquad_warp<S, REV, true, true>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, false, true>(a, ring, band, chan, chunk0, lane);
+    } else {
+        if (edge) biquad_warp<S, REV, true, false>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, false, false>(a, ring, band, chan, chunk0, lane);
     }
 }
 
