@@ -270,31 +270,46 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     };
 
     // ---- pass 1: task t owns the butterflies f0 = t and M1 - t (Hermitian partners) ----
-    for (int t = tid; t < M1 / 2; t += T) {
-        if (t == 0) {      // the two self-mirrored butterflies f0 = 0 and f0 = M1/2
-            double2 z[R1];
+    if (warp == T / 32 - 1) {
+        // task 0: the two self-mirrored butterflies f0 = 0 and f0 = M1/2.  Their 2 R1 inputs are fetched by 2 R1 lanes
+        // at once (one L2 round trip instead of 2 R1 on the CTA's critical path) and handed to lanes 0 and 1; the
+        // last warp has the fewest regular tasks
+        static_assert(2 * R1 <= 32, "special task needs 2 R1 lanes");
+        double2 zf = make_double2(0.0, 0.0);
+        if (lane < 2 * R1) zf = fetch((lane / R1) * (M1 / 2) + M1 * (lane % R1));
+        double2 z[R1];
 #pragma unroll
-            for (int k = 0; k < R1; ++k) z[k] = fetch(M1 * k);
-            pass1_table<S>(z, 0, sm, g.tw);
-#pragma unroll
-            for (int k = 0; k < R1; ++k) z[k] = fetch(M1 / 2 + M1 * k);
-            pass1_table<S>(z, M1 / 2, sm, g.tw);
-            continue;
+        for (int k = 0; k < R1; ++k) {
+            z[k].x = __shfl_sync(0xffffffffu, zf.x, k + R1 * (lane & 1));
+            z[k].y = __shfl_sync(0xffffffffu, zf.y, k + R1 * (lane & 1));
         }
-        double2 zA[R1], zB[R1];
-        // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd)
+        if (lane < 2) pass1_table<S>(z, lane * (M1 / 2), sm, g.tw);
+    }
+    {
+        // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd); otherwise its
+        // mirror L - f is loaded: two base offsets per task, the rest are immediate offsets
         constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
-        {   // every load of the task is issued before the first use: one L2 round trip per task
-            double2 vi0[R1], vj0[R1], vi1[R1], vj1[R1];
+        double2 vi0[R1], vj0[R1], vi1[R1], vj1[R1], w1;
+        auto load_task = [&](int t) {
+            const int md = t, mm = L - t;
 #pragma unroll
             for (int k = 0; k < R1; ++k) {
-                const int f = t + M1 * k;
-                const int gi = k < HALF ? f : L - f;
+                const int gi = k < HALF ? md + M1 * k : mm - M1 * k;
                 vi0[k] = ldg2(Xi0 + gi);
                 vj0[k] = ldg2(Xj0 + gi);
                 vj1[k] = has1 ? ldg2(Xj1 + gi) : make_double2(0.0, 0.0);
                 vi1[k] = same_i ? vi0[k] : ldg2(Xi1 + gi);
             }
+            w1 = ldg2(g.tw + t);
+        };
+        // software pipeline: the loads of the task after this one are in flight while this one's butterflies run.
+        // The prefetch buffer is 4 R1 complex registers: affordable up to R1 = 8; beyond, load then use.
+        constexpr bool PIPE = R1 <= 8;
+        int t = tid == 0 ? T : tid;      // task 0 is the special one above
+        if (PIPE && t < M1 / 2) load_task(t);
+        while (t < M1 / 2) {
+            if (!PIPE) load_task(t);
+            double2 zA[R1], zB[R1], W[R1];
 #pragma unroll
             for (int k = 0; k < R1; ++k) {
                 const bool direct = k < HALF;
@@ -304,14 +319,16 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
                 zA[k] = direct ? zg : zm;
                 zB[(R1 - k) % R1] = direct ? zm : zg;      // slot R1-1-k, rotated by one (see store_pair)
             }
+            W[0] = make_double2(1.0, 0.0);
+            if constexpr (R1 > 1) W[1] = w1;
+            const int tn = t + T;
+            if (PIPE && tn < M1 / 2) load_task(tn);
+            Dft<R1>::run(zA);
+            Dft<R1>::run(zB);
+            powers<R1>(W);
+            store_pair<S, 0>(zA, zB, W, t, sm);
+            t = tn;
         }
-        Dft<R1>::run(zA);
-        Dft<R1>::run(zB);
-        double2 W[R1];
-        W[0] = make_double2(1.0, 0.0);
-        if constexpr (R1 > 1) W[1] = ldg2(g.tw + t);
-        powers<R1>(W);
-        store_pair<S, 0>(zA, zB, W, t, sm);
     }
     __syncthreads();
     pass2<S, T>(sm, g.tw, tid);
