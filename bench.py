@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c3")
     ap.add_argument("--hours", type=float, default=None, help="record length per GPU (default: the workload's)")
-    ap.add_argument("--method", default="auto", choices=["auto", "direct", "fft"])
+    ap.add_argument("--method", default="auto", choices=["auto", "direct", "fft", "fft64", "fft32"])
     ap.add_argument("--max-lag", type=int, default=-1, help="restrict |lag| (default: all 2N-1 lags = reference)")
     ap.add_argument("--cpu-sample-min", type=float, default=3.0, help="minutes of record for the CPU legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -142,7 +142,8 @@ def run_b200(args):
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     j = workload(args)
-    method = {"auto": _capi.XCORR_AUTO, "direct": _capi.XCORR_DIRECT, "fft": _capi.XCORR_FFT}[args.method]
+    method = {"auto": _capi.XCORR_AUTO, "direct": _capi.XCORR_DIRECT, "fft": _capi.XCORR_FFT, "fft64": _capi.XCORR_FFT,
+              "fft32": _capi.XCORR_FFT32}[args.method]
     fs, nchan, nb = j["fs"], j["nchans"], j["nbands"]
     g_npts = j["npts_per_gpu"] * world                       # weak scaling: N x the record length
     sos = np.stack([design_sos(j["filter_type"], *band_edges(j["freqlist"], b, "log"), fs, j["filter_order"],
@@ -329,7 +330,7 @@ def main():
     for b in range(B):
         W, N = int(plan.win_count[b]), int(plan.win_len[b])
         L = 0
-        if args.method != "direct" and (args.method == "fft" or N >= 128):
+        if args.method != "direct" and (args.method in ("fft", "fft64", "fft32") or N >= 128):
             L = int(lib.nbls_xcorr_fft_length(N, args.max_lag))
         if L:      # FFT path: ceil(C/2) forward + ceil(P/2) inverse complex FFTs of L points (5 L log2 L each),
             n_fft_bands += 1       # cross-spectra 2 x 6 flop and arg-max 2 compares per point of the inverse

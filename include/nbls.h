@@ -47,6 +47,9 @@ extern "C" {
 #define NBLS_XCORR_AUTO 0
 #define NBLS_XCORR_DIRECT 1 /* time-domain FP64 contraction over the circularly padded window */
 #define NBLS_XCORR_FFT 2    /* shared-memory FP64 FFT + exact re-evaluation of near-tied lags */
+#define NBLS_XCORR_FFT32 3  /* FP32 FFT screens the lags, every candidate within 2e-5 of the FP32 maximum is
+                               evaluated exactly (FP64 time-domain sums); lags and cmax are FP64 results.
+                               NBLS_XCORR_AUTO picks this wherever the FFT path applies. */
 
 typedef struct nbls_ctx nbls_ctx;
 
@@ -100,6 +103,13 @@ int nbls_xcorr(nbls_ctx* ctx, const nbls_window_desc* win, const double* y_dev, 
  * nbls_window_desc); 0 if the FFT path does not cover that window length (NBLS_XCORR_AUTO then runs the
  * time-domain kernel).  Pure host arithmetic, needs no context. */
 int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag);
+
+/* Diagnostics of the cross-correlation calls since the context was created (or last reset): candidate lags
+ * evaluated exactly by the FP32-screen path, (window, pair) items handed to the time-domain kernel (near-ties,
+ * non-finite data, screen/exact disagreement), and the largest |FP32 screen maximum - exact maximum| seen
+ * (normalised correlation units; the screen's candidate band is 2e-5).  Synchronises.  Any pointer may be NULL. */
+int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain, double* max_screen_err,
+                     int32_t reset);
 
 /* ---- K3: per-window statistics and slowness solve ---------------------------------- */
 typedef struct nbls_solve_desc {

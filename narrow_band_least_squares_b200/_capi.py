@@ -20,7 +20,7 @@ c_int32_p = C.POINTER(C.c_int32)
 c_int64_p = C.POINTER(C.c_int64)
 c_uint8_p = C.POINTER(C.c_uint8)
 
-XCORR_AUTO, XCORR_DIRECT, XCORR_FFT = 0, 1, 2
+XCORR_AUTO, XCORR_DIRECT, XCORR_FFT, XCORR_FFT32 = 0, 1, 2, 3
 
 
 class FilterDesc(C.Structure):
@@ -75,6 +75,7 @@ EXPORTS = {
     "nbls_xcorr": (C.c_int, [C.c_void_p, C.POINTER(WindowDesc), C.c_void_p, C.c_int32, C.c_int64, C.c_int64,
                              C.c_void_p, C.c_void_p]),
     "nbls_xcorr_fft_length": (C.c_int, [C.c_int32, C.c_int32]),
+    "nbls_xcorr_stats": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p, c_double_p, C.c_int32]),
     "nbls_solve": (C.c_int, [C.c_void_p, C.POINTER(SolveDesc), C.c_int64, C.c_void_p, C.c_void_p,
                              C.POINTER(Outputs)]),
     "nbls_run_device": (C.c_int, [C.c_void_p, C.POINTER(Job), C.c_void_p, C.c_int32, C.c_int64, C.c_int64,

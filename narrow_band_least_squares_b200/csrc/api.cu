@@ -70,16 +70,19 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
         int method = w->method;
         // AUTO: the FFT path wherever it applies and the window is long enough for N log N to win
         if (method == NBLS_XCORR_AUTO)
-            method = (N >= 128 && xcorr_fft_length(N, w->max_lag) > 0) ? NBLS_XCORR_FFT : NBLS_XCORR_DIRECT;
-        if (method == NBLS_XCORR_FFT && xcorr_fft_length(N, w->max_lag) == 0) {
+            method = (N >= 128 && xcorr_fft_length(N, w->max_lag) > 0) ? NBLS_XCORR_FFT32 : NBLS_XCORR_DIRECT;
+        NBLS_REQUIRE(method == NBLS_XCORR_DIRECT || method == NBLS_XCORR_FFT || method == NBLS_XCORR_FFT32,
+                     "nbls_xcorr: unknown method %d", method);
+        if (method != NBLS_XCORR_DIRECT && xcorr_fft_length(N, w->max_lag) == 0) {
             set_error("nbls_xcorr: FFT path does not support windows of %d samples", N);
             return NBLS_ERR_UNSUPPORTED;
         }
         int32_t* lb = lag + row * P;
         double* cb = cmax ? cmax + row * P : nullptr;
         const double* yb = y + (int64_t)b * ystride_band;
-        if (method == NBLS_XCORR_FFT)
-            NBLS_CHECK(xcorr_fft_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb));
+        if (method != NBLS_XCORR_DIRECT)
+            NBLS_CHECK(xcorr_fft_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb,
+                                      method == NBLS_XCORR_FFT32));
         else
             NBLS_CHECK(xcorr_direct_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb,
                                          nullptr, nullptr, 0));
@@ -255,7 +258,7 @@ int nbls_destroy(nbls_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->coef, &ctx->state, &ctx->carry, &ctx->taper, &ctx->filt, &ctx->geom, &ctx->lts_tab,
                       &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch, &ctx->spec,
-                      &ctx->energy, &ctx->flags};
+                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& kv : ctx->fft_tw)
@@ -356,6 +359,26 @@ int nbls_xcorr(nbls_ctx* ctx, const nbls_window_desc* win, const double* y_dev, 
 }
 
 int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag) { return xcorr_fft_length(win_len, max_lag); }
+
+int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain, double* max_screen_err, int32_t reset) {
+    NBLS_REQUIRE(ctx, "nbls_xcorr_stats: null context");
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (ctx->xstat.p) {
+        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+        NBLS_CUDA(cudaMemcpy(h, ctx->xstat.p, sizeof(h), cudaMemcpyDeviceToHost));
+        if (reset) NBLS_CUDA(cudaMemset(ctx->xstat.p, 0, sizeof(h)));
+    }
+    if (n_verified) *n_verified = (int64_t)h[0];
+    if (n_time_domain) *n_time_domain = (int64_t)h[1];
+    if (max_screen_err) {
+        const unsigned int bits = (unsigned int)h[2];
+        float f;
+        memcpy(&f, &bits, sizeof(f));
+        *max_screen_err = (double)f;
+    }
+    return NBLS_OK;
+}
 
 int nbls_solve(nbls_ctx* ctx, const nbls_solve_desc* sol, int64_t nwin, const int32_t* lag_dev, const double* cmax_dev,
                const nbls_outputs* out_dev) {

@@ -1,5 +1,5 @@
-// fft_radix.cuh — register-resident FP64 DFT butterflies (radix 2..32, factors 2 and 3) used by the
-// shared-memory FFT of xcorr_fft.cu.  All transforms have the INVERSE sign, e^{+2 pi i kn/R}, and
+// fft_radix.cuh — register-resident DFT butterflies (radix 2..32, factors 2 and 3) used by the
+// shared-memory FFTs of xcorr_fft.cu, written once for complex FP64 (double2) and complex FP32 (float2).  All transforms have the INVERSE sign, e^{+2 pi i kn/R}, and
 // are unnormalised; every index is a compile-time constant after unrolling so the operands stay in
 // registers and trivial twiddles (1, i, -1, -i) cost nothing.
 #pragma once
@@ -45,29 +45,45 @@ constexpr double cos96(int k) {
 }
 constexpr double sin96(int k) { return cos96(k - 24); }
 
-__device__ __forceinline__ double2 cadd(double2 a, double2 b) { return make_double2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ double2 csub(double2 a, double2 b) { return make_double2(a.x - b.x, a.y - b.y); }
-__device__ __forceinline__ double2 cconj(double2 a) { return make_double2(a.x, -a.y); }
-__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
-    return make_double2(fma(a.x, b.x, -(a.y * b.y)), fma(a.x, b.y, a.y * b.x));
+// complex helpers for both precisions: V is double2 or float2, real_t<V> its component type
+template <class V> struct real_of;
+template <> struct real_of<double2> { typedef double type; };
+template <> struct real_of<float2> { typedef float type; };
+template <class V> using real_t = typename real_of<V>::type;
+template <class F> struct cplx_of;
+template <> struct cplx_of<double> { typedef double2 type; };
+template <> struct cplx_of<float> { typedef float2 type; };
+template <class F> using cplx_t = typename cplx_of<F>::type;
+
+__device__ __forceinline__ double2 mk2(double x, double y) { return make_double2(x, y); }
+__device__ __forceinline__ float2 mk2(float x, float y) { return make_float2(x, y); }
+__device__ __forceinline__ double fmad(double a, double b, double c) { return fma(a, b, c); }
+__device__ __forceinline__ float fmad(float a, float b, float c) { return fmaf(a, b, c); }
+
+template <class V> __device__ __forceinline__ V cadd(V a, V b) { return mk2(a.x + b.x, a.y + b.y); }
+template <class V> __device__ __forceinline__ V csub(V a, V b) { return mk2(a.x - b.x, a.y - b.y); }
+template <class V> __device__ __forceinline__ V cconj(V a) { return mk2(a.x, -a.y); }
+template <class V> __device__ __forceinline__ V cmul(V a, V b) {
+    return mk2(fmad(a.x, b.x, -(a.y * b.y)), fmad(a.x, b.y, a.y * b.x));
 }
 // a * conj(b)
-__device__ __forceinline__ double2 cmulc(double2 a, double2 b) {
-    return make_double2(fma(a.x, b.x, a.y * b.y), fma(a.y, b.x, -(a.x * b.y)));
+template <class V> __device__ __forceinline__ V cmulc(V a, V b) {
+    return mk2(fmad(a.x, b.x, a.y * b.y), fmad(a.y, b.x, -(a.x * b.y)));
 }
 
 // v * e^{+2 pi i NUM/DEN}, DEN | 96
-template <int NUM, int DEN>
-__device__ __forceinline__ double2 mul_root(double2 v) {
+template <int NUM, int DEN, class V>
+__device__ __forceinline__ V mul_root(V v) {
+    typedef real_t<V> F;
     static_assert(96 % DEN == 0, "root order must divide 96");
     constexpr int k = mod96(NUM * (96 / DEN));
     if constexpr (k == 0) return v;
-    else if constexpr (k == 24) return make_double2(-v.y, v.x);
-    else if constexpr (k == 48) return make_double2(-v.x, -v.y);
-    else if constexpr (k == 72) return make_double2(v.y, -v.x);
+    else if constexpr (k == 24) return mk2(-v.y, v.x);
+    else if constexpr (k == 48) return mk2(-v.x, -v.y);
+    else if constexpr (k == 72) return mk2(v.y, -v.x);
     else {
-        constexpr double c = cos96(k), s = sin96(k);
-        return make_double2(fma(c, v.x, -(s * v.y)), fma(c, v.y, s * v.x));
+        constexpr F c = (F)cos96(k), s = (F)sin96(k);
+        return mk2(fmad(c, v.x, -(s * v.y)), fmad(c, v.y, s * v.x));
     }
 }
 
@@ -75,19 +91,20 @@ template <int R>
 struct Dft {
     static_assert(R % 2 == 0, "radix must be 2^a or 3*2^a");
     // decimation in time: even/odd halves, then one layer of radix-2 butterflies
-    static __device__ __forceinline__ void run(double2 (&v)[R]) {
+    template <class V>
+    static __device__ __forceinline__ void run(V (&v)[R]) {
         constexpr int H = R / 2;
-        double2 e[H], o[H];
+        V e[H], o[H];
 #pragma unroll
         for (int k = 0; k < H; ++k) { e[k] = v[2 * k]; o[k] = v[2 * k + 1]; }
         Dft<H>::run(e);
         Dft<H>::run(o);
         combine<0>(v, e, o);
     }
-    template <int N>
-    static __device__ __forceinline__ void combine(double2 (&v)[R], const double2 (&e)[R / 2], const double2 (&o)[R / 2]) {
+    template <int N, class V>
+    static __device__ __forceinline__ void combine(V (&v)[R], const V (&e)[R / 2], const V (&o)[R / 2]) {
         if constexpr (N < R / 2) {
-            const double2 t = mul_root<N, R>(o[N]);
+            const V t = mul_root<N, R>(o[N]);
             v[N] = cadd(e[N], t);
             v[N + R / 2] = csub(e[N], t);
             combine<N + 1>(v, e, o);
@@ -96,23 +113,27 @@ struct Dft {
 };
 template <>
 struct Dft<1> {
-    static __device__ __forceinline__ void run(double2 (&)[1]) {}
+    template <class V>
+    static __device__ __forceinline__ void run(V (&)[1]) {}
 };
 template <>
 struct Dft<2> {
-    static __device__ __forceinline__ void run(double2 (&v)[2]) {
-        const double2 a = v[0], b = v[1];
+    template <class V>
+    static __device__ __forceinline__ void run(V (&v)[2]) {
+        const V a = v[0], b = v[1];
         v[0] = cadd(a, b);
         v[1] = csub(a, b);
     }
 };
 template <>
 struct Dft<3> {
-    static __device__ __forceinline__ void run(double2 (&v)[3]) {
-        const double2 t = cadd(v[1], v[2]), d = csub(v[1], v[2]);
-        const double2 m = make_double2(fma(-0.5, t.x, v[0].x), fma(-0.5, t.y, v[0].y));
-        constexpr double s = Q96[8];   // sin 120 deg
-        const double2 ie = make_double2(-s * d.y, s * d.x);          // i * s * d
+    template <class V>
+    static __device__ __forceinline__ void run(V (&v)[3]) {
+        typedef real_t<V> F;
+        const V t = cadd(v[1], v[2]), d = csub(v[1], v[2]);
+        const V m = mk2(fmad((F)-0.5, t.x, v[0].x), fmad((F)-0.5, t.y, v[0].y));
+        constexpr F s = (F)Q96[8];   // sin 120 deg
+        const V ie = mk2(-s * d.y, s * d.x);          // i * s * d
         v[0] = cadd(v[0], t);
         v[1] = cadd(m, ie);
         v[2] = csub(m, ie);
@@ -120,9 +141,10 @@ struct Dft<3> {
 };
 template <>
 struct Dft<4> {
-    static __device__ __forceinline__ void run(double2 (&v)[4]) {
-        const double2 a = cadd(v[0], v[2]), b = csub(v[0], v[2]), c = cadd(v[1], v[3]), d = csub(v[1], v[3]);
-        const double2 id = make_double2(-d.y, d.x);
+    template <class V>
+    static __device__ __forceinline__ void run(V (&v)[4]) {
+        const V a = cadd(v[0], v[2]), b = csub(v[0], v[2]), c = cadd(v[1], v[3]), d = csub(v[1], v[3]);
+        const V id = mk2(-d.y, d.x);
         v[0] = cadd(a, c);
         v[2] = csub(a, c);
         v[1] = cadd(b, id);
@@ -131,8 +153,8 @@ struct Dft<4> {
 };
 
 // W[n] = W[1]^n for n = 2..R-1 by a balanced product tree (depth <= log2 R roundings)
-template <int R, int N = 2>
-__device__ __forceinline__ void powers(double2 (&W)[R]) {
+template <int R, int N = 2, class V>
+__device__ __forceinline__ void powers(V (&W)[R]) {
     if constexpr (N < R) {
         W[N] = cmul(W[N / 2], W[N - N / 2]);
         powers<R, N + 1>(W);

@@ -1,5 +1,11 @@
 // xcorr_fft.cu — K2 (frequency domain): windowed pairwise cross-correlation over the co-array through
-// shared-memory FP64 FFTs, with an on-chip arg-max and an exactness guard.
+// shared-memory FFTs, with an on-chip arg-max and an exactness guard.  Two flavours share the code:
+//   NBLS_XCORR_FFT32 (default)  FP32 FFTs SCREEN the 2N-1 lags: every lag whose FP32 value lies within
+//                    XF_TAU32 of the FP32 maximum (>= 50x the FP32 pipeline's worst observed error) is a
+//                    candidate - one lag for ~95 % of the pair-windows - and xf_verify_kernel evaluates the
+//                    candidates EXACTLY (FP64 time-domain sums over the staged windows), so the integer
+//                    lag and cmax come from FP64 arithmetic on the original samples.
+//   NBLS_XCORR_FFT   FP64 FFTs decide directly; near-ties (gap < XF_TAU) go to the time-domain kernel.
 //
 // Replaces LsBeam.correlate (lts_array/lts_array/classes/lts_classes.py:852-880 of the reference):
 // cij = np.correlate(x_i, x_j, 'full') / sqrt(Ei*Ej); delay = argmax(cij); cmax = max(cij).
@@ -39,7 +45,10 @@ namespace nbls {
 
 using namespace fft;
 
-constexpr double XF_TAU = 1e-10;   // near-tie threshold, normalised correlation units
+constexpr double XF_TAU = 1e-10;   // FP64 FFT: near-tie threshold, normalised correlation units
+constexpr float XF_TAU32 = 2e-5f;  // FP32 screen: candidate band below the FP32 maximum (error seen: <= 4e-7)
+constexpr int XF_KC = 4;           // candidate lags kept per pair-window (more -> time-domain kernel)
+constexpr int XV_WARPS = 16;       // warps of a verification CTA
 
 struct XfArgs {
     const double* y;      // band base, [C] rows of stride ldy
@@ -50,13 +59,17 @@ struct XfArgs {
     int w0, wn;           // windows [w0, w0+wn) of the band are processed by this launch
     int lag_max;
     int SP;               // spectrum row length L/2+1
-    const double2* tw;    // [L] e^{+2 pi i k/L}
-    double2* spec;        // [wn][C][SP]
+    const void* tw;       // [L] e^{+2 pi i k/L}, complex of the transform's precision
+    void* spec;           // [wn][C][SP] complex of the transform's precision
     double* energy;       // [wn][C]
     int32_t* lag;         // [W][P] band level
     double* cmax;         // [W][P] or nullptr
     int* flag_list;       // [>= wn*P] items w*P+p (band level) to re-evaluate in the time domain
     int* flag_count;
+    int32_t* cand;        // FP32 screen: [wn*P][XF_KC] candidate lags of batch item wl*P+p, INT_MIN = unused
+    float* sval;          // FP32 screen: [wn*P] the FP32 maximum (normalised)
+    unsigned long long* stat;   // [0] candidates verified, [1] items sent to the time-domain kernel,
+                                // [2] max |FP32 max - exact max| as float bits
 };
 
 template <int R1_, int R2_, int R3_>
@@ -76,30 +89,32 @@ struct Shape {
 };
 
 __device__ __forceinline__ double2 ldg2(const double2* p) { return __ldg(p); }
+__device__ __forceinline__ float2 ldg2(const float2* p) { return __ldg(p); }
 
 // pass 1 tail: radix-R1 butterfly of the inputs f0 + M1*k, twiddle from the table, store
-template <class S>
-__device__ __forceinline__ void pass1_table(double2 (&z)[S::R1], int f0, double2* sm, const double2* tw) {
+template <class S, class V>
+__device__ __forceinline__ void pass1_table(V (&z)[S::R1], int f0, V* sm, const V* tw) {
     Dft<S::R1>::run(z);
 #pragma unroll
     for (int n1 = 0; n1 < S::R1; ++n1) {
-        const double2 v = n1 == 0 ? z[0] : cmul(z[n1], ldg2(tw + f0 * n1));
+        const V v = n1 == 0 ? z[0] : cmul(z[n1], ldg2(tw + f0 * n1));
         sm[S::pad(n1 * S::M1 + f0)] = v;
     }
 }
 
 // pass 2: radix-R2 butterflies inside every sub-transform, in place
-template <class S, int T>
-__device__ __forceinline__ void pass2(double2* sm, const double2* tw, int tid) {
+template <class S, int T, class V>
+__device__ __forceinline__ void pass2(V* sm, const V* tw, int tid) {
+    typedef real_t<V> F;
     for (int u = tid; u < S::L / S::R2; u += T) {
         const int n1 = u / S::M2, f1 = u - n1 * S::M2;
-        double2* base = sm + S::ROW * (n1 * S::R2) + f1;
-        double2 z[S::R2];
+        V* base = sm + S::ROW * (n1 * S::R2) + f1;
+        V z[S::R2];
 #pragma unroll
         for (int k = 0; k < S::R2; ++k) z[k] = base[S::ROW * k];
         // twiddles w_L^{R1 f1 n2} = W1^n2: one table entry, the powers by a product tree
-        double2 Wp[S::R2];
-        Wp[0] = make_double2(1.0, 0.0);
+        V Wp[S::R2];
+        Wp[0] = mk2((F)1, (F)0);
         Wp[1] = ldg2(tw + S::R1 * f1);
         Dft<S::R2>::run(z);
         powers<S::R2>(Wp);
@@ -111,10 +126,12 @@ __device__ __forceinline__ void pass2(double2* sm, const double2* tw, int tid) {
 // ---- spectra kernel -------------------------------------------------------------------------
 // grid = wn * ceil(C/2); CTA (w, cp) transforms channels a = 2cp and b = 2cp+1 of window w.
 // Forward DFT through the inverse machinery: Y = IDFT(conj z)  =>  Z = conj(Y).
-template <class S, int T, int MINB>
+template <class S, int T, int MINB, class V>
 __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
-    extern __shared__ __align__(16) double2 xf_smem[];
-    double2* sm = xf_smem;
+    typedef real_t<V> F;
+    extern __shared__ __align__(16) unsigned char xf_smem_raw[];
+    V* sm = reinterpret_cast<V*>(xf_smem_raw);
+    const V* tw = static_cast<const V*>(g.tw);
     __shared__ double red[2][T / 32];
     __shared__ double rs_sh[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -153,23 +170,24 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     __syncthreads();
     const double rsa = rs_sh[0], rsb = rs_sh[1];
 
-    // pass 1: inputs conj(z)[n] = (x_a[n], -x_b[n]) * scale, zero beyond the window
+    // pass 1: inputs conj(z)[n] = (x_a[n], -x_b[n]) * scale, zero beyond the window (scaled in FP64, then
+    // rounded to the transform's precision)
     for (int f0 = tid; f0 < S::M1; f0 += T) {
-        double2 z[S::R1];
+        V z[S::R1];
 #pragma unroll
         for (int k = 0; k < S::R1; ++k) {
             const int n = f0 + S::M1 * k;
-            z[k] = n < g.N ? make_double2(xa[n] * rsa, -(xb[n] * rsb)) : make_double2(0.0, 0.0);
+            z[k] = n < g.N ? mk2((F)(xa[n] * rsa), (F)(-(xb[n] * rsb))) : mk2((F)0, (F)0);
         }
-        pass1_table<S>(z, f0, sm, g.tw);
+        pass1_table<S>(z, f0, sm, tw);
     }
     __syncthreads();
-    pass2<S, T>(sm, g.tw, tid);
+    pass2<S, T>(sm, tw, tid);
     __syncthreads();
     // pass 3 in place
     for (int u = tid; u < S::L / S::R3; u += T) {
-        double2* base = sm + S::ROW * u;
-        double2 z[S::R3];
+        V* base = sm + S::ROW * u;
+        V z[S::R3];
 #pragma unroll
         for (int k = 0; k < S::R3; ++k) z[k] = base[k];
         Dft<S::R3>::run(z);
@@ -178,13 +196,14 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     }
     __syncthreads();
     // unpack: X_a[f] = (conj(Y[f]) + Y[L-f]) / 2,  X_b[f] = (conj(Y[f]) - Y[L-f]) / (2i)
-    double2* Xa = g.spec + ((int64_t)wl * g.C + ca) * g.SP;
-    double2* Xb = g.spec + ((int64_t)wl * g.C + cb) * g.SP;
+    V* Xa = static_cast<V*>(g.spec) + ((int64_t)wl * g.C + ca) * g.SP;
+    V* Xb = static_cast<V*>(g.spec) + ((int64_t)wl * g.C + cb) * g.SP;
+    constexpr F half = (F)0.5;
     for (int f = tid; f <= S::L / 2; f += T) {
-        const double2 yf = sm[S::pos(f)];
-        const double2 ym = sm[S::pos(f == 0 ? 0 : S::L - f)];
-        Xa[f] = make_double2(0.5 * (yf.x + ym.x), 0.5 * (ym.y - yf.y));
-        if (has_b) Xb[f] = make_double2(-0.5 * (yf.y + ym.y), -0.5 * (yf.x - ym.x));
+        const V yf = sm[S::pos(f)];
+        const V ym = sm[S::pos(f == 0 ? 0 : S::L - f)];
+        Xa[f] = mk2(half * (yf.x + ym.x), half * (ym.y - yf.y));
+        if (has_b) Xb[f] = mk2(-half * (yf.y + ym.y), -half * (yf.x - ym.x));
     }
 }
 
@@ -214,13 +233,14 @@ __device__ __forceinline__ void pair_channels(int p, int C, int& ci, int& cj) {
     ci = i;
     cj = i + 1 + rem;
 }
+__device__ __forceinline__ int pair_index(int ci, int cj, int C) { return ci * (2 * C - ci - 1) / 2 + (cj - ci - 1); }
 
 // pass-1 stores of the partner butterflies f0 = t (A) and M1 - t (B); W[n] = w_L^{t n}, so B's twiddle
 // is w_L^{(M1-t) n} = e^{2 pi i n/R1} conj(W[n]); the constant factor e^{2 pi i n/R1} was applied for free
 // by feeding B's inputs to the butterfly rotated by one position (DFT shift theorem)
-template <class S, int N1>
-__device__ __forceinline__ void store_pair(const double2 (&zA)[S::R1], const double2 (&zB)[S::R1],
-                                           const double2 (&W)[S::R1], int t, double2* sm) {
+template <class S, int N1, class V>
+__device__ __forceinline__ void store_pair(const V (&zA)[S::R1], const V (&zB)[S::R1], const V (&W)[S::R1], int t,
+                                           V* sm) {
     if constexpr (N1 < S::R1) {
         if constexpr (N1 == 0) {
             sm[S::pad(t)] = zA[0];
@@ -234,12 +254,13 @@ __device__ __forceinline__ void store_pair(const double2 (&zA)[S::R1], const dou
 }
 
 // grid = wn * ceil(P/2); CTA (w, q) correlates pairs 2q (real part) and 2q+1 (imaginary part)
-template <class S, int T, int MINB>
+template <class S, int T, int MINB, class V>
 __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
-    extern __shared__ __align__(16) double2 xf_smem[];
-    double2* sm = xf_smem;
-    __shared__ double rb1[2][T / 32], rb2[2][T / 32];
-    __shared__ int rl1[2][T / 32];
+    typedef real_t<V> F;
+    constexpr bool SCREEN = sizeof(F) == 4;
+    extern __shared__ __align__(16) unsigned char xf_smem_raw[];
+    V* sm = reinterpret_cast<V*>(xf_smem_raw);
+    const V* tw = static_cast<const V*>(g.tw);
     constexpr int R1 = S::R1, L = S::L, M1 = S::M1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int npp = (g.P + 1) >> 1;
@@ -249,47 +270,74 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     int i0, j0, i1, j1;
     pair_channels(p0, g.C, i0, j0);
     pair_channels(has1 ? p1 : p0, g.C, i1, j1);
-    const double2* sbase = g.spec + (int64_t)wl * g.C * g.SP;
-    const double2 *Xi0 = sbase + (int64_t)i0 * g.SP, *Xj0 = sbase + (int64_t)j0 * g.SP;
-    const double2 *Xi1 = sbase + (int64_t)i1 * g.SP, *Xj1 = sbase + (int64_t)j1 * g.SP;
+    const V* sbase = static_cast<const V*>(g.spec) + (int64_t)wl * g.C * g.SP;
+    const V *Xi0 = sbase + (int64_t)i0 * g.SP, *Xj0 = sbase + (int64_t)j0 * g.SP;
+    const V *Xi1 = sbase + (int64_t)i1 * g.SP, *Xj1 = sbase + (int64_t)j1 * g.SP;
     const bool same_i = i0 == i1;
 
     // cross-spectra of entry gidx: a = X_i0 conj(X_j0), b = X_i1 conj(X_j1)
-    auto cross = [&](int gidx, double2& a, double2& b) {
-        const double2 xi = ldg2(Xi0 + gidx);
+    auto cross = [&](int gidx, V& a, V& b) {
+        const V xi = ldg2(Xi0 + gidx);
         a = cmulc(xi, ldg2(Xj0 + gidx));
         if (has1) b = cmulc(same_i ? xi : ldg2(Xi1 + gidx), ldg2(Xj1 + gidx));
-        else b = make_double2(0.0, 0.0);
+        else b = mk2((F)0, (F)0);
     };
     // Z[f] for any f in [0, L): Z = a + i b on the stored half, conj(a) + i conj(b) on the mirrored one
-    auto fetch = [&](int f) -> double2 {
-        double2 a, b;
-        if (f <= L / 2) { cross(f, a, b); return make_double2(a.x - b.y, a.y + b.x); }
+    auto fetch = [&](int f) -> V {
+        V a, b;
+        if (f <= L / 2) { cross(f, a, b); return mk2(a.x - b.y, a.y + b.x); }
         cross(L - f, a, b);
-        return make_double2(a.x + b.y, b.x - a.y);
+        return mk2(a.x + b.y, b.x - a.y);
     };
 
+    if constexpr (SCREEN) {
+        // ---- FP32: cross-spectra straight into shared memory (natural order; every load independent, so the L2
+        // latency is hidden by memory-level parallelism), then a plain in-place radix-R1 pass.  Register use stays
+        // low enough for 24 warps per SM. ----
+#pragma unroll 4
+        for (int f = tid; f <= L / 2; f += T) {
+            const V xi = ldg2(Xi0 + f), xj = ldg2(Xj0 + f);
+            const V yj = has1 ? ldg2(Xj1 + f) : mk2((F)0, (F)0);
+            const V yi = same_i ? xi : ldg2(Xi1 + f);
+            const V a = cmulc(xi, xj), b = cmulc(yi, yj);
+            sm[S::pad(f)] = mk2(a.x - b.y, a.y + b.x);                    // Z[f]   = a + i b
+            if (f != 0 && f != L / 2) sm[S::pad(L - f)] = mk2(a.x + b.y, b.x - a.y);   // Z[L-f] = conj(a) + i conj(b)
+        }
+        __syncthreads();
+        for (int f0 = tid; f0 < M1; f0 += T) {
+            V z[R1], W[R1];
+            V* base = sm + S::pad(f0);           // pad(f0 + M1 k) = pad(f0) + k (M1 + R2)
+#pragma unroll
+            for (int k = 0; k < R1; ++k) z[k] = base[k * (M1 + S::R2)];
+            W[0] = mk2((F)1, (F)0);
+            if constexpr (R1 > 1) W[1] = ldg2(tw + f0);
+            Dft<R1>::run(z);
+            powers<R1>(W);
+#pragma unroll
+            for (int n1 = 0; n1 < R1; ++n1) base[n1 * (M1 + S::R2)] = n1 == 0 ? z[0] : cmul(z[n1], W[n1]);
+        }
+    } else {
     // ---- pass 1: task t owns the butterflies f0 = t and M1 - t (Hermitian partners) ----
     if (warp == T / 32 - 1) {
         // task 0: the two self-mirrored butterflies f0 = 0 and f0 = M1/2.  Their 2 R1 inputs are fetched by 2 R1 lanes
         // at once (one L2 round trip instead of 2 R1 on the CTA's critical path) and handed to lanes 0 and 1; the
         // last warp has the fewest regular tasks
         static_assert(2 * R1 <= 32, "special task needs 2 R1 lanes");
-        double2 zf = make_double2(0.0, 0.0);
+        V zf = mk2((F)0, (F)0);
         if (lane < 2 * R1) zf = fetch((lane / R1) * (M1 / 2) + M1 * (lane % R1));
-        double2 z[R1];
+        V z[R1];
 #pragma unroll
         for (int k = 0; k < R1; ++k) {
             z[k].x = __shfl_sync(0xffffffffu, zf.x, k + R1 * (lane & 1));
             z[k].y = __shfl_sync(0xffffffffu, zf.y, k + R1 * (lane & 1));
         }
-        if (lane < 2) pass1_table<S>(z, lane * (M1 / 2), sm, g.tw);
+        if (lane < 2) pass1_table<S>(z, lane * (M1 / 2), sm, tw);
     }
     {
         // f = t + M1 k lies in the stored half iff k < R1/2 (R1 even) or k <= (R1-1)/2 (R1 odd); otherwise its
         // mirror L - f is loaded: two base offsets per task, the rest are immediate offsets
         constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
-        double2 vi0[R1], vj0[R1], vi1[R1], vj1[R1], w1;
+        V vi0[R1], vj0[R1], vi1[R1], vj1[R1], w1;
         auto load_task = [&](int t) {
             const int md = t, mm = L - t;
 #pragma unroll
@@ -297,29 +345,29 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
                 const int gi = k < HALF ? md + M1 * k : mm - M1 * k;
                 vi0[k] = ldg2(Xi0 + gi);
                 vj0[k] = ldg2(Xj0 + gi);
-                vj1[k] = has1 ? ldg2(Xj1 + gi) : make_double2(0.0, 0.0);
+                vj1[k] = has1 ? ldg2(Xj1 + gi) : mk2((F)0, (F)0);
                 vi1[k] = same_i ? vi0[k] : ldg2(Xi1 + gi);
             }
-            w1 = ldg2(g.tw + t);
+            w1 = ldg2(tw + t);
         };
         // software pipeline: the loads of the task after this one are in flight while this one's butterflies run.
-        // The prefetch buffer is 4 R1 complex registers: affordable up to R1 = 8; beyond, load then use.
-        constexpr bool PIPE = R1 <= 8;
+        // The prefetch buffer is 4 R1 complex registers: affordable up to R1 = 8 (FP64) / 12 (FP32); beyond, load then use.
+        constexpr bool PIPE = R1 <= (SCREEN ? 12 : 8);
         int t = tid == 0 ? T : tid;      // task 0 is the special one above
         if (PIPE && t < M1 / 2) load_task(t);
         while (t < M1 / 2) {
             if (!PIPE) load_task(t);
-            double2 zA[R1], zB[R1], W[R1];
+            V zA[R1], zB[R1], W[R1];
 #pragma unroll
             for (int k = 0; k < R1; ++k) {
                 const bool direct = k < HALF;
-                const double2 a = cmulc(vi0[k], vj0[k]), b = cmulc(vi1[k], vj1[k]);
-                const double2 zg = make_double2(a.x - b.y, a.y + b.x);     // Z[g]
-                const double2 zm = make_double2(a.x + b.y, b.x - a.y);     // Z[L-g]
+                const V a = cmulc(vi0[k], vj0[k]), b = cmulc(vi1[k], vj1[k]);
+                const V zg = mk2(a.x - b.y, a.y + b.x);     // Z[g]
+                const V zm = mk2(a.x + b.y, b.x - a.y);     // Z[L-g]
                 zA[k] = direct ? zg : zm;
                 zB[(R1 - k) % R1] = direct ? zm : zg;      // slot R1-1-k, rotated by one (see store_pair)
             }
-            W[0] = make_double2(1.0, 0.0);
+            W[0] = mk2((F)1, (F)0);
             if constexpr (R1 > 1) W[1] = w1;
             const int tn = t + T;
             if (PIPE && tn < M1 / 2) load_task(tn);
@@ -330,16 +378,101 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             t = tn;
         }
     }
+    }
     __syncthreads();
-    pass2<S, T>(sm, g.tw, tid);
+    pass2<S, T>(sm, tw, tid);
     // with R2 = R3 = 32 and one warp per n1, a warp's pass-3 rows are exactly the rows it wrote in pass 2
     if constexpr (S::R2 == 32 && S::R3 == 32 && T == 32 * R1) __syncwarp();
     else __syncthreads();
 
+    const int lag_max = g.lag_max;
+    constexpr int STEP = R1 * S::R2;
+    if constexpr (SCREEN) {
+        // ---- pass 3 + screening from registers: the FP32 maximum over the wanted lags, then every lag within
+        // XF_TAU32 of it becomes a candidate for the exact FP64 evaluation (xf_verify_kernel) ----
+        static_assert(T * S::R3 >= L, "at most one pass-3 row per thread");
+        __shared__ float smax[2][T / 32];
+        __shared__ int scnt[2];
+        __shared__ int scl[2][XF_KC];
+        const bool act = tid < L / S::R3;     // T is a multiple of 32, the row count need not be
+        const int u = act ? tid : 0;
+        V z[S::R3];
+        {
+            const V* base = sm + S::ROW * u;
+#pragma unroll
+            for (int k = 0; k < S::R3; ++k) z[k] = base[k];
+        }
+        Dft<S::R3>::run(z);
+        const int n1 = u / S::R2, n2 = u - n1 * S::R2;
+        const int nb = n1 + R1 * n2;
+        // circular index n = nb + R1 R2 n3 stands for lag n (n <= lag_max) or n - L (n >= L - lag_max): the wanted
+        // n3 are [0, n3a] and [n3b, R3)
+        const int n3a = !act ? -1 : (lag_max >= nb ? (lag_max - nb) / STEP : -1);
+        const int n3b = !act ? S::R3 : (max(L - lag_max - nb, 0) + STEP - 1) / STEP;
+        const float NEG = -CUDART_INF_F;
+        float mr = NEG, mi = NEG;
+#pragma unroll
+        for (int n3 = 0; n3 < S::R3; ++n3) {
+            const bool ok = (n3 <= n3a) | (n3 >= n3b);
+            mr = fmaxf(mr, ok ? z[n3].x : NEG);
+            mi = fmaxf(mi, ok ? z[n3].y : NEG);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mr = fmaxf(mr, __shfl_xor_sync(0xffffffffu, mr, o));
+            mi = fmaxf(mi, __shfl_xor_sync(0xffffffffu, mi, o));
+        }
+        if (lane == 0) { smax[0][warp] = mr; smax[1][warp] = mi; }
+        if (tid < 2) scnt[tid] = 0;
+        __syncthreads();
+        mr = smax[0][0]; mi = smax[1][0];
+#pragma unroll
+        for (int i = 1; i < T / 32; ++i) { mr = fmaxf(mr, smax[0][i]); mi = fmaxf(mi, smax[1][i]); }
+        const float thr_r = mr - XF_TAU32 * (float)L, thr_i = mi - XF_TAU32 * (float)L;
+#pragma unroll
+        for (int n3 = 0; n3 < S::R3; ++n3) {
+            const bool ok = (n3 <= n3a) | (n3 >= n3b);
+            const bool hr = ok & (z[n3].x >= thr_r), hi = ok & (z[n3].y >= thr_i);
+            if (hr | hi) {
+                const int n = nb + STEP * n3;
+                const int lg = n <= lag_max ? n : n - L;
+                if (hr) { const int s_ = atomicAdd(&scnt[0], 1); if (s_ < XF_KC) scl[0][s_] = lg; }
+                if (hi) { const int s_ = atomicAdd(&scnt[1], 1); if (s_ < XF_KC) scl[1][s_] = lg; }
+            }
+        }
+        __syncthreads();
+        if (tid < 2 && (tid == 0 || has1)) {
+            const int p = tid == 0 ? p0 : p1;
+            const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
+            const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
+            const double den = sqrt(Ei * Ej);
+            const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+            const int64_t loc = (int64_t)wl * g.P + p;
+            const int cnt = scnt[tid];
+            int32_t* cd = g.cand + loc * XF_KC;
+            bool give = false;
+            if (!(den > 0.0)) {
+                // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched
+                g.lag[item] = -lag_max;
+                if (g.cmax) g.cmax[item] = __longlong_as_double(0x7ff8000000000000LL);
+            } else if (!isfinite(den) || cnt < 1 || cnt > XF_KC) {
+                // non-finite data, or too many near-tied lags: the time-domain kernel evaluates every lag
+                const int slot = atomicAdd(g.flag_count, 1);
+                g.flag_list[slot] = (int)item;
+                atomicAdd(g.stat + 1, 1ULL);
+            } else {
+                give = true;
+            }
+#pragma unroll
+            for (int s_ = 0; s_ < XF_KC; ++s_) cd[s_] = (give && s_ < cnt) ? scl[tid][s_] : INT_MIN;
+            g.sval[loc] = (tid == 0 ? mr : mi) / (float)L;
+        }
+    } else {
     // ---- pass 3 + arg-max straight from registers ----
+    __shared__ double rb1[2][T / 32], rb2[2][T / 32];
+    __shared__ int rl1[2][T / 32];
     constexpr int NCH = 4;     // independent arg-max chains per component (the update is a serial dependency)
     Top accr = {-CUDART_INF, -CUDART_INF, INT_MAX}, acci = {-CUDART_INF, -CUDART_INF, INT_MAX};
-    const int lag_max = g.lag_max;
     for (int u = tid; u < L / S::R3; u += T) {
         Top tr[NCH], ti[NCH];
 #pragma unroll
@@ -347,8 +480,8 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             tr[c].b1 = tr[c].b2 = ti[c].b1 = ti[c].b2 = -CUDART_INF;
             tr[c].l1 = ti[c].l1 = INT_MAX;
         }
-        const double2* base = sm + S::ROW * u;
-        double2 z[S::R3];
+        const V* base = sm + S::ROW * u;
+        V z[S::R3];
 #pragma unroll
         for (int k = 0; k < S::R3; ++k) z[k] = base[k];
         Dft<S::R3>::run(z);
@@ -356,7 +489,6 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         const int nb = n1 + R1 * n2;
         // circular index n = nb + R1 R2 n3 stands for lag n (n <= lag_max) or n - L (n >= L - lag_max): the wanted
         // n3 are [0, n3a] and [n3b, R3); the chains record n3, the lag is rebuilt afterwards
-        constexpr int STEP = R1 * S::R2;
         const int n3a = lag_max >= nb ? (lag_max - nb) / STEP : -1;
         const int n3b = (max(L - lag_max - nb, 0) + STEP - 1) / STEP;
 #pragma unroll
@@ -405,8 +537,122 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             if (!(b.b1 - b.b2 > XF_TAU * (double)L) || !isfinite(den)) {
                 const int slot = atomicAdd(g.flag_count, 1);
                 g.flag_list[slot] = (int)item;
+                atomicAdd(g.stat + 1, 1ULL);
             }
         }
+    }
+    }
+}
+
+// ---- verification kernel (FP32 screen only) -------------------------------------------------
+// Exact FP64 value of every candidate lag: c[k] = sum_n x_i[n+k] x_j[n] over the original filtered samples.
+// grid = wn * ceil((C-1)/IB); CTA (w, ib) stages the windows of channels i = IB ib .. IB ib + IB-1 in shared
+// memory; each warp takes channels j > i in turn, streams x_j once from L2 and accumulates the first candidate
+// of the (up to IB) pairs (i, j) together; further candidates (near-ties, ~5 % of the pairs) are evaluated one
+// by one.  The largest exact value wins, the lowest lag on an exact tie (np.argmax); cmax = value / sqrt(Ei Ej).
+template <int IB>
+__global__ void __launch_bounds__(XV_WARPS * 32) xf_verify_kernel(XfArgs g) {
+    extern __shared__ __align__(16) unsigned char xf_smem_raw[];
+    double* xs = reinterpret_cast<double*>(xf_smem_raw);     // [IB][N]
+    __shared__ float werr[XV_WARPS];
+    __shared__ unsigned int wcnt[XV_WARPS];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nib = (g.C - 1 + IB - 1) / IB;
+    const int wl = blockIdx.x / nib, ib = blockIdx.x - wl * nib;
+    const int i_base = ib * IB;
+    const int N = g.N;
+    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+#pragma unroll
+    for (int ii = 0; ii < IB; ++ii) {
+        const int ci = i_base + ii;
+        if (ci < g.C - 1) {
+            const double* src = g.y + (int64_t)ci * g.ldy + t0;
+            for (int n = tid; n < N; n += XV_WARPS * 32) xs[ii * N + n] = __ldg(src + n);
+        }
+    }
+    __syncthreads();
+    float err = 0.f;
+    unsigned int ncand = 0;
+    for (int j = i_base + 1 + warp; j < g.C; j += XV_WARPS) {
+        const double* xj = g.y + (int64_t)j * g.ldy + t0;
+        int k[IB];
+        bool val[IB];
+        const int32_t* cd[IB];
+#pragma unroll
+        for (int ii = 0; ii < IB; ++ii) {
+            const int ci = i_base + ii;
+            val[ii] = ci < j;
+            const int p = pair_index(val[ii] ? ci : 0, j, g.C);
+            cd[ii] = g.cand + ((int64_t)wl * g.P + p) * XF_KC;
+            k[ii] = val[ii] ? cd[ii][0] : INT_MIN;
+            val[ii] = k[ii] != INT_MIN;
+            if (!val[ii]) k[ii] = 0;
+        }
+        double acc[IB];
+#pragma unroll
+        for (int ii = 0; ii < IB; ++ii) acc[ii] = 0.0;
+#pragma unroll 8
+        for (int n = lane; n < N; n += 32) {
+            const double xv = __ldg(xj + n);
+#pragma unroll
+            for (int ii = 0; ii < IB; ++ii) {
+                const int idx = n + k[ii];
+                const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
+                acc[ii] = fma(a, xv, acc[ii]);
+            }
+        }
+#pragma unroll
+        for (int ii = 0; ii < IB; ++ii) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc[ii] += __shfl_xor_sync(0xffffffffu, acc[ii], o);
+        }
+#pragma unroll
+        for (int ii = 0; ii < IB; ++ii) {
+            if (!val[ii]) continue;           // warp-uniform
+            double best = acc[ii];
+            int bl = k[ii];
+            ++ncand;
+            for (int s_ = 1; s_ < XF_KC; ++s_) {
+                const int ks = cd[ii][s_];
+                if (ks == INT_MIN) break;
+                double d = 0.0;
+                for (int n = lane; n < N; n += 32) {
+                    const int idx = n + ks;
+                    const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
+                    d = fma(a, __ldg(xj + n), d);
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+                if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
+                ++ncand;
+            }
+            if (lane == 0) {
+                const int ci = i_base + ii;
+                const int p = pair_index(ci, j, g.C);
+                const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
+                const double c = best / sqrt(Ei * Ej);
+                const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+                g.lag[item] = bl;
+                if (g.cmax) g.cmax[item] = c;
+                // consistency guard: the exact maximum must sit where the screen saw it
+                const float e = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
+                if (!(e <= 0.25f * XF_TAU32)) {
+                    const int slot = atomicAdd(g.flag_count, 1);
+                    g.flag_list[slot] = (int)item;
+                    atomicAdd(g.stat + 1, 1ULL);
+                } else {
+                    err = fmaxf(err, e);
+                }
+            }
+        }
+    }
+    if (lane == 0) { werr[warp] = err; wcnt[warp] = ncand; }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long n = 0;
+        for (int i = 0; i < XV_WARPS; ++i) { err = fmaxf(err, werr[i]); n += wcnt[i]; }
+        atomicAdd(g.stat, n);
+        atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(err));
     }
 }
 
@@ -418,71 +664,90 @@ struct XfPlan {
     xf_kernel spectra, pair;
 };
 
-template <int R1, int R2, int R3, int T, int MINB>
+template <class V, int R1, int R2, int R3, int T, int MINB>
 static XfPlan make_plan() {
     using S = Shape<R1, R2, R3>;
     XfPlan p;
     p.L = S::L;
     p.threads = T;
-    p.smem = (size_t)S::SMEM_ELEMS * sizeof(double2);
-    p.spectra = xf_spectra_kernel<S, T, MINB>;
-    p.pair = xf_pair_kernel<S, T, MINB>;
+    p.smem = (size_t)S::SMEM_ELEMS * sizeof(V);
+    p.spectra = xf_spectra_kernel<S, T, MINB, V>;
+    p.pair = xf_pair_kernel<S, T, MINB, V>;
     return p;
 }
 
 // transform lengths 2^a and 3*2^a from 512 to 12288 (192 KB of complex FP64 is what one SM holds)
-static const std::vector<XfPlan>& plans() {
-    static const std::vector<XfPlan> v = {
-        make_plan<2, 16, 16, 32, 4>(),   make_plan<3, 16, 16, 64, 4>(),   make_plan<4, 16, 16, 64, 4>(),
-        make_plan<6, 16, 16, 96, 4>(),   make_plan<8, 16, 16, 128, 3>(),  make_plan<12, 16, 16, 192, 2>(),
-        make_plan<16, 16, 16, 256, 2>(), make_plan<6, 32, 32, 192, 2>(),  make_plan<8, 32, 32, 256, 1>(),
-        make_plan<12, 32, 32, 384, 1>(),
+static const std::vector<XfPlan>& plans(bool fp32) {
+    static const std::vector<XfPlan> v64 = {
+        make_plan<double2, 2, 16, 16, 32, 4>(),   make_plan<double2, 3, 16, 16, 64, 4>(),
+        make_plan<double2, 4, 16, 16, 64, 4>(),   make_plan<double2, 6, 16, 16, 96, 4>(),
+        make_plan<double2, 8, 16, 16, 128, 3>(),  make_plan<double2, 12, 16, 16, 192, 2>(),
+        make_plan<double2, 16, 16, 16, 256, 2>(), make_plan<double2, 6, 32, 32, 192, 2>(),
+        make_plan<double2, 8, 32, 32, 256, 1>(),  make_plan<double2, 12, 32, 32, 384, 1>(),
     };
-    return v;
+    static const std::vector<XfPlan> v32 = {
+        make_plan<float2, 2, 16, 16, 32, 8>(),    make_plan<float2, 3, 16, 16, 64, 8>(),
+        make_plan<float2, 4, 16, 16, 64, 8>(),    make_plan<float2, 6, 16, 16, 96, 8>(),
+        make_plan<float2, 8, 16, 16, 128, 6>(),   make_plan<float2, 12, 16, 16, 192, 4>(),
+        make_plan<float2, 16, 16, 16, 256, 3>(),  make_plan<float2, 6, 32, 32, 192, 4>(),
+        make_plan<float2, 8, 32, 32, 256, 3>(),   make_plan<float2, 12, 32, 32, 384, 2>(),
+    };
+    return fp32 ? v32 : v64;
 }
 
-static const XfPlan* pick_plan(int N, int max_lag) {
+static const XfPlan* pick_plan(int N, int max_lag, bool fp32) {
     if (N < 1) return nullptr;
     const int lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
     const int need = N + lag_max;          // circular length with no wrap-around inside |lag| <= lag_max
-    for (const XfPlan& p : plans())
+    for (const XfPlan& p : plans(fp32))
         if (p.L >= need) return &p;
     return nullptr;
 }
 
 int xcorr_fft_length(int N, int max_lag) {
-    const XfPlan* p = pick_plan(N, max_lag);
+    const XfPlan* p = pick_plan(N, max_lag, false);
     return p ? p->L : 0;
 }
 
-static int twiddles(nbls_ctx* ctx, int L, const double2** out) {
-    auto it = ctx->fft_tw.find(L);
-    if (it != ctx->fft_tw.end()) { *out = (const double2*)it->second; return NBLS_OK; }
-    std::vector<double2> h(L);
+template <class V>
+static int twiddles(nbls_ctx* ctx, int L, const void** out) {
+    const int key = sizeof(V) == sizeof(float2) ? -L : L;
+    auto it = ctx->fft_tw.find(key);
+    if (it != ctx->fft_tw.end()) { *out = it->second; return NBLS_OK; }
+    std::vector<V> h(L);
     const long double two_pi = 6.283185307179586476925286766559005768L;
     for (int k = 0; k < L; ++k) {
-        // reduce to the first octant so that symmetric entries are exact mirror images
         const long double a = two_pi * (long double)k / (long double)L;
-        h[k] = make_double2((double)cosl(a), (double)sinl(a));
+        h[k].x = (real_t<V>)cosl(a);
+        h[k].y = (real_t<V>)sinl(a);
     }
     void* d = nullptr;
-    cudaError_t e = cudaMalloc(&d, (size_t)L * sizeof(double2));
+    cudaError_t e = cudaMalloc(&d, (size_t)L * sizeof(V));
     if (e != cudaSuccess) {
         cudaGetLastError();
         set_error("nbls_xcorr(fft): twiddle table allocation failed: %s", cudaGetErrorString(e));
         return NBLS_ERR_NOMEM;
     }
-    NBLS_CUDA(cudaMemcpyAsync(d, h.data(), (size_t)L * sizeof(double2), cudaMemcpyHostToDevice, ctx->stream));
+    NBLS_CUDA(cudaMemcpyAsync(d, h.data(), (size_t)L * sizeof(V), cudaMemcpyHostToDevice, ctx->stream));
     NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->fft_tw[L] = d;
-    *out = (const double2*)d;
+    ctx->fft_tw[key] = d;
+    *out = d;
     return NBLS_OK;
 }
 
+typedef void (*xv_kernel)(XfArgs);
+static xv_kernel pick_verify(int N, size_t smem_optin, int* ib) {
+    const size_t row = (size_t)N * sizeof(double);
+    if (4 * row <= smem_optin - 1024) { *ib = 4; return xf_verify_kernel<4>; }
+    if (2 * row <= smem_optin - 1024) { *ib = 2; return xf_verify_kernel<2>; }
+    if (row <= smem_optin - 1024) { *ib = 1; return xf_verify_kernel<1>; }
+    return nullptr;
+}
+
 int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                   int max_lag, int32_t* lag, double* cmax) {
+                   int max_lag, int32_t* lag, double* cmax, bool fp32) {
     if (W <= 0) return NBLS_OK;
-    const XfPlan* pl = pick_plan(N, max_lag);
+    const XfPlan* pl = pick_plan(N, max_lag, fp32);
     if (!pl) {
         set_error("nbls_xcorr(fft): no transform length for a window of %d samples", N);
         return NBLS_ERR_UNSUPPORTED;
@@ -493,10 +758,20 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     NBLS_REQUIRE((int64_t)W * P < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld",
                  (long long)W * P);
     const int SP = pl->L / 2 + 1;
-    const double2* tw = nullptr;
-    NBLS_CHECK(twiddles(ctx, pl->L, &tw));
+    const void* tw = nullptr;
+    if (fp32) NBLS_CHECK(twiddles<float2>(ctx, pl->L, &tw));
+    else NBLS_CHECK(twiddles<double2>(ctx, pl->L, &tw));
+    int ib = 0;
+    xv_kernel verify = nullptr;
+    size_t vsmem = 0;
+    if (fp32) {
+        verify = pick_verify(N, ctx->smem_optin, &ib);
+        NBLS_REQUIRE(verify, "nbls_xcorr(fft32): a window of %d samples does not fit in shared memory", N);
+        vsmem = (size_t)ib * N * sizeof(double);
+        NBLS_CUDA(cudaFuncSetAttribute(verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
+    }
     // windows per batch: spectra workspace bounded (they are re-read from L2 window by window)
-    const size_t per_win = (size_t)C * SP * sizeof(double2);
+    const size_t per_win = (size_t)C * SP * (fp32 ? sizeof(float2) : sizeof(double2));
     const size_t budget = (size_t)4 << 30;
     const int ncp = (C + 1) / 2, npp = (P + 1) / 2;
     int wb = (int)std::min<int64_t>(W, std::max<int64_t>(1, (int64_t)(budget / per_win)));
@@ -504,6 +779,14 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     NBLS_CHECK(ensure(ctx, ctx->spec, (size_t)wb * per_win));
     NBLS_CHECK(ensure(ctx, ctx->energy, (size_t)wb * C * sizeof(double)));
     NBLS_CHECK(ensure(ctx, ctx->flags, ((size_t)wb * P + 4) * sizeof(int)));
+    if (!ctx->xstat.p) {
+        NBLS_CHECK(ensure(ctx, ctx->xstat, 4 * sizeof(unsigned long long)));
+        NBLS_CUDA(cudaMemsetAsync(ctx->xstat.p, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    }
+    if (fp32) {
+        NBLS_CHECK(ensure(ctx, ctx->cand, (size_t)wb * P * XF_KC * sizeof(int32_t)));
+        NBLS_CHECK(ensure(ctx, ctx->sval, (size_t)wb * P * sizeof(float)));
+    }
     NBLS_CUDA(cudaFuncSetAttribute(pl->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
     NBLS_CUDA(cudaFuncSetAttribute(pl->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
 
@@ -512,11 +795,14 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first;
     a.lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
     a.SP = SP; a.tw = tw;
-    a.spec = (double2*)ctx->spec.p;
+    a.spec = ctx->spec.p;
     a.energy = (double*)ctx->energy.p;
     a.lag = lag; a.cmax = cmax;
     a.flag_count = (int*)ctx->flags.p;
     a.flag_list = a.flag_count + 4;
+    a.cand = (int32_t*)ctx->cand.p;
+    a.sval = (float*)ctx->sval.p;
+    a.stat = (unsigned long long*)ctx->xstat.p;
     for (int w0 = 0; w0 < W; w0 += wb) {
         a.w0 = w0;
         a.wn = std::min(wb, W - w0);
@@ -526,7 +812,13 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         pl->pair<<<(unsigned)(a.wn * npp), pl->threads, pl->smem, ctx->stream>>>(a);
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 2;
-        // near-tied arg-maxima are settled by the time-domain kernel (normally an empty list)
+        if (fp32) {
+            const int nib = (C - 1 + ib - 1) / ib;
+            verify<<<(unsigned)(a.wn * nib), XV_WARPS * 32, vsmem, ctx->stream>>>(a);
+            NBLS_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+        }
+        // undecided arg-maxima are settled by the time-domain kernel (normally an empty list)
         NBLS_CHECK(xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
                                      ctx->sm_count * 2));
     }

@@ -225,6 +225,13 @@ class Engine:
         check(self.lib.nbls_measure_fp64_peak(self.ctx, int(iters), C.byref(v)))
         return v.value
 
+    def xcorr_stats(self, reset=False):
+        """Diagnostics of the FP32-screen cross-correlation (nbls_xcorr_stats): candidates verified exactly, items the
+        time-domain kernel settled, largest |FP32 screen maximum - exact maximum| seen."""
+        nv, nt, err = C.c_int64(), C.c_int64(), C.c_double()
+        check(self.lib.nbls_xcorr_stats(self.ctx, C.byref(nv), C.byref(nt), C.byref(err), int(bool(reset))))
+        return dict(verified=nv.value, time_domain=nt.value, max_screen_err=err.value)
+
     # ---- stage level ------------------------------------------------------------------------
     def filter_bands(self, data, fs, sos_list, zerophase=True, taper=0.01, chunk_len=0, exact_scan=False,
                      global_t0=0, global_npts=None):

@@ -71,7 +71,8 @@ def test_filter_matches_oracle(eng, name):
             assert np.allclose(out[b][:, :64], g[f"b{b}_filt_head"], rtol=0, atol=1e-12 * float(rms.max()))
 
 
-@pytest.mark.parametrize("method", [_capi.XCORR_DIRECT, _capi.XCORR_FFT], ids=["direct", "fft"])
+@pytest.mark.parametrize("method", [_capi.XCORR_DIRECT, _capi.XCORR_FFT, _capi.XCORR_FFT32],
+                         ids=["direct", "fft64", "fft32"])
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_xcorr_lags_bit_exact(eng, name, method):
     g, rec, _, pkw = _case(name)
@@ -158,7 +159,7 @@ def test_ltsva_surface_and_restricted_lag(eng):
     n, hop, starts = orc.window_grid(rec.npts, rec.fs, float(g["winlen_list"][0]), float(g["winover"]))
     pairs, *_ = orc.co_array(g["b0_rij"])
     ref_lag, ref_cmax, *_ = orc.correlate_windows(np.ascontiguousarray(filt.T), starts, n, rec.fs, pairs, None, L)
-    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT):
+    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT, _capi.XCORR_FFT32):
         lag, cmax = eng.xcorr(filt[None], [n], [hop], [len(starts)], max_lag=L, method=method)
         assert np.array_equal(lag.T, ref_lag), method
         assert np.allclose(cmax.T, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
@@ -187,14 +188,15 @@ def test_xcorr_fft_ties_and_unequal_amplitudes(eng):
     x[3] = np.roll(x[2], 7) * 1e-15 + rng.standard_normal(t) * 1e-16   # weak rider, delayed copy
     x[4] = 0.0                            # dead channel
     ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
-    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT):
+    for method in (_capi.XCORR_DIRECT, _capi.XCORR_FFT, _capi.XCORR_FFT32):
         lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=method)
         assert np.array_equal(lag, ref_lag), method
         assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-12, equal_nan=True), method
 
 
+@pytest.mark.parametrize("method", [_capi.XCORR_FFT, _capi.XCORR_FFT32], ids=["fft64", "fft32"])
 @pytest.mark.parametrize("n", [128, 255, 384, 700, 1023, 1200, 1537, 2048, 3000, 3100, 4097, 6000, 6144])
-def test_xcorr_fft_every_transform_length(eng, n):
+def test_xcorr_fft_every_transform_length(eng, n, method):
     """One window length per transform size (512 ... 12288 points), odd channel and pair counts."""
     rng = np.random.default_rng(n)
     c, count = 5, 3
@@ -203,12 +205,32 @@ def test_xcorr_fft_every_transform_length(eng, n):
     s = rng.standard_normal(t + 64)
     x = np.stack([s[k * 3:k * 3 + t] + 0.5 * rng.standard_normal(t) for k in range(c)])
     ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
-    lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=_capi.XCORR_FFT)
+    lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=method)
     assert np.array_equal(lag, ref_lag)
     assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
-    lag2, _ = eng.xcorr(x[None], [n], [hop], [count], max_lag=n // 10, method=_capi.XCORR_FFT)
+    lag2, _ = eng.xcorr(x[None], [n], [hop], [count], max_lag=n // 10, method=method)
     ref2, _ = _oracle_xcorr(x, n, hop, count, max_lag=n // 10)
     assert np.array_equal(lag2, ref2)
+
+
+def test_xcorr_fp32_screen_statistics(eng):
+    """The FP32 screen hands ~1 candidate per pair-window to the exact FP64 evaluation and its maximum agrees with the
+    exact one far inside the candidate band (2e-5): the margin that makes the integer lags FP64-exact."""
+    rng = np.random.default_rng(11)
+    n, hop, count, c = 3000, 1500, 12, 7
+    t = n + hop * (count - 1)
+    s = rng.standard_normal(t + 64)
+    x = np.stack([s[k * 2:k * 2 + t] + 0.3 * rng.standard_normal(t) for k in range(c)])
+    eng.xcorr_stats(reset=True)
+    lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=_capi.XCORR_FFT32)
+    st = eng.xcorr_stats(reset=True)
+    ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
+    assert np.array_equal(lag, ref_lag)
+    assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-13)
+    items = count * c * (c - 1) // 2
+    assert items <= st["verified"] <= 1.5 * items, st
+    assert st["time_domain"] == 0, st
+    assert 0.0 < st["max_screen_err"] < 2e-6, st
 
 
 def test_errors_mirror_reference(eng):
