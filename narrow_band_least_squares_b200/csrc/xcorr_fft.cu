@@ -425,19 +425,22 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         if (lane == 0) { smax[0][warp] = mr; smax[1][warp] = mi; }
         if (tid < 2) scnt[tid] = 0;
         __syncthreads();
+        const float lmr = mr, lmi = mi;       // warp-level maxima
         mr = smax[0][0]; mi = smax[1][0];
 #pragma unroll
         for (int i = 1; i < T / 32; ++i) { mr = fmaxf(mr, smax[0][i]); mi = fmaxf(mi, smax[1][i]); }
         const float thr_r = mr - XF_TAU32 * (float)L, thr_i = mi - XF_TAU32 * (float)L;
+        if ((lmr >= thr_r) | (lmi >= thr_i)) {      // warp-uniform: only warps holding a value inside the band rescan
 #pragma unroll
-        for (int n3 = 0; n3 < S::R3; ++n3) {
-            const bool ok = (n3 <= n3a) | (n3 >= n3b);
-            const bool hr = ok & (z[n3].x >= thr_r), hi = ok & (z[n3].y >= thr_i);
-            if (hr | hi) {
-                const int n = nb + STEP * n3;
-                const int lg = n <= lag_max ? n : n - L;
-                if (hr) { const int s_ = atomicAdd(&scnt[0], 1); if (s_ < XF_KC) scl[0][s_] = lg; }
-                if (hi) { const int s_ = atomicAdd(&scnt[1], 1); if (s_ < XF_KC) scl[1][s_] = lg; }
+            for (int n3 = 0; n3 < S::R3; ++n3) {
+                const bool ok = (n3 <= n3a) | (n3 >= n3b);
+                const bool hr = ok & (z[n3].x >= thr_r), hi = ok & (z[n3].y >= thr_i);
+                if (hr | hi) {
+                    const int n = nb + STEP * n3;
+                    const int lg = n <= lag_max ? n : n - L;
+                    if (hr) { const int s_ = atomicAdd(&scnt[0], 1); if (s_ < XF_KC) scl[0][s_] = lg; }
+                    if (hi) { const int s_ = atomicAdd(&scnt[1], 1); if (s_ < XF_KC) scl[1][s_] = lg; }
+                }
             }
         }
         __syncthreads();
@@ -567,6 +570,7 @@ __global__ void __launch_bounds__(XV_WARPS * 32) xf_verify_kernel(XfArgs g) {
         const int ci = i_base + ii;
         if (ci < g.C - 1) {
             const double* src = g.y + (int64_t)ci * g.ldy + t0;
+#pragma unroll 8
             for (int n = tid; n < N; n += XV_WARPS * 32) xs[ii * N + n] = __ldg(src + n);
         }
     }
@@ -591,8 +595,23 @@ __global__ void __launch_bounds__(XV_WARPS * 32) xf_verify_kernel(XfArgs g) {
         double acc[IB];
 #pragma unroll
         for (int ii = 0; ii < IB; ++ii) acc[ii] = 0.0;
-#pragma unroll 8
-        for (int n = lane; n < N; n += 32) {
+        constexpr int U = 8;                 // x_j loads in flight per lane
+        int n = lane;
+        for (; n + 32 * (U - 1) < N; n += 32 * U) {
+            double xv[U];
+#pragma unroll
+            for (int q = 0; q < U; ++q) xv[q] = __ldg(xj + n + 32 * q);
+#pragma unroll
+            for (int q = 0; q < U; ++q) {
+#pragma unroll
+                for (int ii = 0; ii < IB; ++ii) {
+                    const int idx = n + 32 * q + k[ii];
+                    const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
+                    acc[ii] = fma(a, xv[q], acc[ii]);
+                }
+            }
+        }
+        for (; n < N; n += 32) {
             const double xv = __ldg(xj + n);
 #pragma unroll
             for (int ii = 0; ii < IB; ++ii) {
