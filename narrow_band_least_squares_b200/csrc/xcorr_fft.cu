@@ -48,7 +48,6 @@ using namespace fft;
 constexpr double XF_TAU = 1e-10;   // FP64 FFT: near-tie threshold, normalised correlation units
 constexpr float XF_TAU32 = 2e-5f;  // FP32 screen: candidate band below the FP32 maximum (error seen: <= 4e-7)
 constexpr int XF_KC = 4;           // candidate lags kept per pair-window (more -> time-domain kernel)
-constexpr int XV_WARPS = 16;       // warps of a verification CTA
 
 struct XfArgs {
     const double* y;      // band base, [C] rows of stride ldy
@@ -550,21 +549,83 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
 // ---- verification kernel (FP32 screen only) -------------------------------------------------
 // Exact FP64 value of every candidate lag: c[k] = sum_n x_i[n+k] x_j[n] over the original filtered samples.
 // grid = wn * ceil((C-1)/IB); CTA (w, ib) stages the windows of channels i = IB ib .. IB ib + IB-1 in shared
-// memory; each warp takes channels j > i in turn, streams x_j once from L2 and accumulates the first candidate
-// of the (up to IB) pairs (i, j) together; further candidates (near-ties, ~5 % of the pairs) are evaluated one
-// by one.  The largest exact value wins, the lowest lag on an exact tie (np.argmax); cmax = value / sqrt(Ei Ej).
+// memory.  Warp (slice, group) owns one of XV_SL time slices of the window and every XV_JG-th channel j > i: it
+// streams its slice of x_j once from L2 (8 loads in flight per lane) and accumulates the first candidate of the
+// (up to IB) pairs (i, j) together; the part of a slice whose shifted indices all stay inside the window runs
+// without bounds checks.  Slice sums are combined in a fixed order (deterministic); further candidates (near-ties,
+// ~5 % of the pairs) are evaluated warp by warp afterwards.  The largest exact value wins, the lowest lag on an
+// exact tie (np.argmax); cmax = value / sqrt(Ei Ej).
+constexpr int XV_WARPS = 32;
+constexpr int XV_SL = 8;
+constexpr int XV_JG = XV_WARPS / XV_SL;
+static_assert(XF_KC <= 4, "work-list entries pack the candidate slot in two bits");
+
+static size_t verify_smem(int IB, int N, int C) {
+    return (size_t)IB * N * sizeof(double) + (size_t)(C - 1) * IB * (XV_SL + XF_KC - 1) * sizeof(double) +
+           (size_t)(C - 1) * IB * (XF_KC + 1) * sizeof(int) + 16;
+}
+
+// lanes walk [a, b) with stride 32; CHECK: shifted indices may fall outside [0, N) and then contribute 0
+// (rows are addressed as xs[off + n] with INTEGER offsets off = ii N + k: a pointer xs + off formed for a negative
+// lag would lie before the array - undefined behaviour the compiler exploits to "prove" k >= 0)
+template <int IB, bool CHECK>
+__device__ __forceinline__ void verify_slice(const double* xj, const double* xs, const int (&off)[IB], const int (&k)[IB],
+                                             int a, int b, int N, int lane, double (&acc)[IB]) {
+    constexpr int U = 8;
+    int n = a + lane;
+    for (; n + 32 * (U - 1) < b; n += 32 * U) {
+        double xv[U];
+#pragma unroll
+        for (int q = 0; q < U; ++q) xv[q] = __ldg(xj + n + 32 * q);
+#pragma unroll
+        for (int q = 0; q < U; ++q) {
+#pragma unroll
+            for (int ii = 0; ii < IB; ++ii) {
+                double v;
+                if constexpr (CHECK) v = (unsigned)(n + 32 * q + k[ii]) < (unsigned)N ? xs[off[ii] + n + 32 * q] : 0.0;
+                else v = xs[off[ii] + n + 32 * q];
+                acc[ii] = fma(v, xv[q], acc[ii]);
+            }
+        }
+    }
+    for (; n < b; n += 32) {
+        const double xv = __ldg(xj + n);
+#pragma unroll
+        for (int ii = 0; ii < IB; ++ii) {
+            const double v = (!CHECK || (unsigned)(n + k[ii]) < (unsigned)N) ? xs[off[ii] + n] : 0.0;
+            acc[ii] = fma(v, xv, acc[ii]);
+        }
+    }
+}
+
 template <int IB>
-__global__ void __launch_bounds__(XV_WARPS * 32) xf_verify_kernel(XfArgs g) {
+__global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
     extern __shared__ __align__(16) unsigned char xf_smem_raw[];
+    const int N = g.N, NJ = g.C - 1;
     double* xs = reinterpret_cast<double*>(xf_smem_raw);     // [IB][N]
+    double* sp = xs + (size_t)IB * N;                        // [NJ][IB][XV_SL] slice sums of the first candidate
+    double* se = sp + (size_t)NJ * IB * XV_SL;               // [NJ][IB][XF_KC-1] sums of the further candidates
+    int* elist = reinterpret_cast<int*>(se + (size_t)NJ * IB * (XF_KC - 1));   // [NJ*IB*(XF_KC-1)] (jj, ii, s) packed
+    int* k0s = elist + (size_t)NJ * IB * (XF_KC - 1);        // [NJ][IB] first candidate k of pair (i_base+ii, i_base+1+jj),
+    int* nk0s = k0s + (size_t)NJ * IB;                       // 0 if none; and -k (see the note on VIMNMX3 below)
+    __shared__ int ecount;
     __shared__ float werr[XV_WARPS];
     __shared__ unsigned int wcnt[XV_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nib = (g.C - 1 + IB - 1) / IB;
     const int wl = blockIdx.x / nib, ib = blockIdx.x - wl * nib;
     const int i_base = ib * IB;
-    const int N = g.N;
     const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+    if (tid == 0) ecount = 0;
+    const int njj = g.C - 1 - i_base;                    // channels j = i_base+1 .. C-1
+    for (int e = tid; e < njj * IB; e += XV_WARPS * 32) {
+        const int jj = e / IB, ii = e - jj * IB;
+        const int ci = i_base + ii, j = i_base + 1 + jj;
+        int kk = ci < j ? g.cand[((int64_t)wl * g.P + pair_index(ci, j, g.C)) * XF_KC] : INT_MIN;
+        if (kk == INT_MIN) kk = 0;
+        k0s[e] = kk;
+        nk0s[e] = -kk;
+    }
 #pragma unroll
     for (int ii = 0; ii < IB; ++ii) {
         const int ci = i_base + ii;
@@ -575,95 +636,111 @@ __global__ void __launch_bounds__(XV_WARPS * 32) xf_verify_kernel(XfArgs g) {
         }
     }
     __syncthreads();
-    float err = 0.f;
-    unsigned int ncand = 0;
-    for (int j = i_base + 1 + warp; j < g.C; j += XV_WARPS) {
-        const double* xj = g.y + (int64_t)j * g.ldy + t0;
-        int k[IB];
-        bool val[IB];
-        const int32_t* cd[IB];
-#pragma unroll
-        for (int ii = 0; ii < IB; ++ii) {
-            const int ci = i_base + ii;
-            val[ii] = ci < j;
-            const int p = pair_index(val[ii] ? ci : 0, j, g.C);
-            cd[ii] = g.cand + ((int64_t)wl * g.P + p) * XF_KC;
-            k[ii] = val[ii] ? cd[ii][0] : INT_MIN;
-            val[ii] = k[ii] != INT_MIN;
-            if (!val[ii]) k[ii] = 0;
-        }
-        double acc[IB];
-#pragma unroll
-        for (int ii = 0; ii < IB; ++ii) acc[ii] = 0.0;
-        constexpr int U = 8;                 // x_j loads in flight per lane
-        int n = lane;
-        for (; n + 32 * (U - 1) < N; n += 32 * U) {
-            double xv[U];
-#pragma unroll
-            for (int q = 0; q < U; ++q) xv[q] = __ldg(xj + n + 32 * q);
-#pragma unroll
-            for (int q = 0; q < U; ++q) {
-#pragma unroll
-                for (int ii = 0; ii < IB; ++ii) {
-                    const int idx = n + 32 * q + k[ii];
-                    const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
-                    acc[ii] = fma(a, xv[q], acc[ii]);
-                }
-            }
-        }
-        for (; n < N; n += 32) {
-            const double xv = __ldg(xj + n);
+    {
+        const int sl = warp % XV_SL, jg = warp / XV_SL;
+        const int SLN = ((N + XV_SL - 1) / XV_SL + 31) / 32 * 32;
+        const int a = min(N, sl * SLN), b = min(N, a + SLN);
+        for (int j = i_base + 1 + jg; j < g.C; j += XV_JG) {
+            const double* xj = g.y + (int64_t)j * g.ldy + t0;
+            int k[IB], off[IB];
+            int lo = a, hi = b;          // [lo, hi): the part of the slice where every pair's shifted index is inside
 #pragma unroll
             for (int ii = 0; ii < IB; ++ii) {
-                const int idx = n + k[ii];
-                const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
-                acc[ii] = fma(a, xv, acc[ii]);
+                // -k comes from its own shared-memory array: written as max(max(lo, -k0), -k1), ptxas 12.9 (sm_100a) folds
+                // the expression into VIMNMX3 and drops the negation of one operand (seen in SASS and at run time)
+                const int kk = k0s[(j - i_base - 1) * IB + ii], nk = nk0s[(j - i_base - 1) * IB + ii];
+                k[ii] = kk;
+                off[ii] = ii * N + kk;
+                lo = max(lo, nk);
+                hi = min(hi, N + nk);
             }
-        }
+            lo = min(lo, b);
+            hi = max(hi, lo);
+            double acc[IB];
 #pragma unroll
-        for (int ii = 0; ii < IB; ++ii) {
+            for (int ii = 0; ii < IB; ++ii) acc[ii] = 0.0;
+            if (a < lo) verify_slice<IB, true>(xj, xs, off, k, a, lo, N, lane, acc);
+            verify_slice<IB, false>(xj, xs, off, k, lo, hi, N, lane, acc);
+            if (hi < b) verify_slice<IB, true>(xj, xs, off, k, hi, b, N, lane, acc);
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) acc[ii] += __shfl_xor_sync(0xffffffffu, acc[ii], o);
-        }
+            for (int ii = 0; ii < IB; ++ii) {
 #pragma unroll
-        for (int ii = 0; ii < IB; ++ii) {
-            if (!val[ii]) continue;           // warp-uniform
-            double best = acc[ii];
-            int bl = k[ii];
-            ++ncand;
-            for (int s_ = 1; s_ < XF_KC; ++s_) {
-                const int ks = cd[ii][s_];
-                if (ks == INT_MIN) break;
-                double d = 0.0;
-                for (int n = lane; n < N; n += 32) {
-                    const int idx = n + ks;
-                    const double a = (unsigned)idx < (unsigned)N ? xs[ii * N + idx] : 0.0;
-                    d = fma(a, __ldg(xj + n), d);
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-                if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
-                ++ncand;
+                for (int o = 16; o > 0; o >>= 1) acc[ii] += __shfl_xor_sync(0xffffffffu, acc[ii], o);
             }
             if (lane == 0) {
-                const int ci = i_base + ii;
-                const int p = pair_index(ci, j, g.C);
-                const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
-                const double c = best / sqrt(Ei * Ej);
-                const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
-                g.lag[item] = bl;
-                if (g.cmax) g.cmax[item] = c;
-                // consistency guard: the exact maximum must sit where the screen saw it
-                const float e = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
-                if (!(e <= 0.25f * XF_TAU32)) {
-                    const int slot = atomicAdd(g.flag_count, 1);
-                    g.flag_list[slot] = (int)item;
-                    atomicAdd(g.stat + 1, 1ULL);
-                } else {
-                    err = fmaxf(err, e);
-                }
+#pragma unroll
+                for (int ii = 0; ii < IB; ++ii) sp[((j - i_base - 1) * IB + ii) * XV_SL + sl] = acc[ii];
             }
         }
+    }
+    // further candidates -> work list
+    for (int e = tid; e < njj * IB; e += XV_WARPS * 32) {
+        const int jj = e / IB, ii = e - jj * IB;
+        const int ci = i_base + ii, j = i_base + 1 + jj;
+        if (ci < j) {
+            const int32_t* cd = g.cand + ((int64_t)wl * g.P + pair_index(ci, j, g.C)) * XF_KC;
+            if (cd[0] != INT_MIN)
+                for (int s_ = 1; s_ < XF_KC && cd[s_] != INT_MIN; ++s_) elist[atomicAdd(&ecount, 1)] = (e << 2) | s_;
+        }
+    }
+    __syncthreads();
+    const int ne = ecount;
+    for (int q = warp; q < ne; q += XV_WARPS) {
+        const int e = elist[q] >> 2, s_ = elist[q] & 3;
+        const int jj = e / IB, ii = e - jj * IB;
+        const int ci = i_base + ii, j = i_base + 1 + jj;
+        const int ks = g.cand[((int64_t)wl * g.P + pair_index(ci, j, g.C)) * XF_KC + s_];
+        const double* xj = g.y + (int64_t)j * g.ldy + t0;
+        const int offs = ii * N + ks;
+        const int nlo = max(0, -ks), nhi = min(N, N - ks);
+        double d = 0.0;
+#pragma unroll 4
+        for (int n = nlo + lane; n < nhi; n += 32) d = fma(xs[offs + n], __ldg(xj + n), d);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        if (lane == 0) se[e * (XF_KC - 1) + s_ - 1] = d;
+    }
+    __syncthreads();
+    // decide: one thread per pair (i, j) of the block
+    float err = 0.f;
+    unsigned int ncand = 0;
+    for (int e = tid; e < njj * IB; e += XV_WARPS * 32) {
+        const int jj = e / IB, ii = e - jj * IB;
+        const int ci = i_base + ii, j = i_base + 1 + jj;
+        if (ci >= j) continue;
+        const int p = pair_index(ci, j, g.C);
+        const int32_t* cd = g.cand + ((int64_t)wl * g.P + p) * XF_KC;
+        if (cd[0] == INT_MIN) continue;
+        double best = 0.0;
+#pragma unroll
+        for (int sl = 0; sl < XV_SL; ++sl) best += sp[e * XV_SL + sl];
+        int bl = cd[0];
+        ++ncand;
+        for (int s_ = 1; s_ < XF_KC && cd[s_] != INT_MIN; ++s_) {
+            const double d = se[e * (XF_KC - 1) + s_ - 1];
+            const int ks = cd[s_];
+            if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
+            ++ncand;
+        }
+        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
+        const double c = best / sqrt(Ei * Ej);
+        const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+        g.lag[item] = bl;
+        if (g.cmax) g.cmax[item] = c;
+        // consistency guard: the exact maximum must sit where the screen saw it
+        const float ee = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
+        if (!(ee <= 0.25f * XF_TAU32)) {
+            const int slot = atomicAdd(g.flag_count, 1);
+            g.flag_list[slot] = (int)item;
+            atomicAdd(g.stat + 1, 1ULL);
+        } else {
+            err = fmaxf(err, ee);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        err = fmaxf(err, __shfl_xor_sync(0xffffffffu, err, o));
+        ncand += __shfl_xor_sync(0xffffffffu, ncand, o);
     }
     if (lane == 0) { werr[warp] = err; wcnt[warp] = ncand; }
     __syncthreads();
@@ -755,11 +832,10 @@ static int twiddles(nbls_ctx* ctx, int L, const void** out) {
 }
 
 typedef void (*xv_kernel)(XfArgs);
-static xv_kernel pick_verify(int N, size_t smem_optin, int* ib) {
-    const size_t row = (size_t)N * sizeof(double);
-    if (4 * row <= smem_optin - 1024) { *ib = 4; return xf_verify_kernel<4>; }
-    if (2 * row <= smem_optin - 1024) { *ib = 2; return xf_verify_kernel<2>; }
-    if (row <= smem_optin - 1024) { *ib = 1; return xf_verify_kernel<1>; }
+static xv_kernel pick_verify(int N, int C, size_t smem_optin, int* ib) {
+    if (verify_smem(4, N, C) <= smem_optin - 1024) { *ib = 4; return xf_verify_kernel<4>; }
+    if (verify_smem(2, N, C) <= smem_optin - 1024) { *ib = 2; return xf_verify_kernel<2>; }
+    if (verify_smem(1, N, C) <= smem_optin - 1024) { *ib = 1; return xf_verify_kernel<1>; }
     return nullptr;
 }
 
@@ -784,9 +860,9 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     xv_kernel verify = nullptr;
     size_t vsmem = 0;
     if (fp32) {
-        verify = pick_verify(N, ctx->smem_optin, &ib);
+        verify = pick_verify(N, C, ctx->smem_optin, &ib);
         NBLS_REQUIRE(verify, "nbls_xcorr(fft32): a window of %d samples does not fit in shared memory", N);
-        vsmem = (size_t)ib * N * sizeof(double);
+        vsmem = verify_smem(ib, N, C);
         NBLS_CUDA(cudaFuncSetAttribute(verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
     }
     // windows per batch: spectra workspace bounded (they are re-read from L2 window by window)
