@@ -772,21 +772,25 @@ static XfPlan make_plan() {
     return p;
 }
 
-// transform lengths 2^a and 3*2^a from 512 to 12288 (192 KB of complex FP64 is what one SM holds)
+// transform lengths 2^a, 3*2^a and 5*2^a from 512 to 12288 (192 KB of complex FP64 is what one SM holds)
 static const std::vector<XfPlan>& plans(bool fp32) {
     static const std::vector<XfPlan> v64 = {
         make_plan<double2, 2, 16, 16, 32, 4>(),   make_plan<double2, 3, 16, 16, 64, 4>(),
         make_plan<double2, 4, 16, 16, 64, 4>(),   make_plan<double2, 6, 16, 16, 96, 4>(),
-        make_plan<double2, 8, 16, 16, 128, 3>(),  make_plan<double2, 12, 16, 16, 192, 2>(),
-        make_plan<double2, 16, 16, 16, 256, 2>(), make_plan<double2, 6, 32, 32, 192, 2>(),
-        make_plan<double2, 8, 32, 32, 256, 1>(),  make_plan<double2, 12, 32, 32, 384, 1>(),
+        make_plan<double2, 8, 16, 16, 128, 3>(),  make_plan<double2, 10, 16, 16, 160, 2>(),
+        make_plan<double2, 12, 16, 16, 192, 2>(), make_plan<double2, 16, 16, 16, 256, 2>(),
+        make_plan<double2, 10, 16, 32, 160, 2>(), make_plan<double2, 6, 32, 32, 192, 2>(),
+        make_plan<double2, 8, 32, 32, 256, 1>(),  make_plan<double2, 10, 32, 32, 320, 1>(),
+        make_plan<double2, 12, 32, 32, 384, 1>(),
     };
     static const std::vector<XfPlan> v32 = {
         make_plan<float2, 2, 16, 16, 32, 8>(),    make_plan<float2, 3, 16, 16, 64, 8>(),
         make_plan<float2, 4, 16, 16, 64, 8>(),    make_plan<float2, 6, 16, 16, 96, 8>(),
-        make_plan<float2, 8, 16, 16, 128, 6>(),   make_plan<float2, 12, 16, 16, 192, 4>(),
-        make_plan<float2, 16, 16, 16, 256, 3>(),  make_plan<float2, 6, 32, 32, 192, 4>(),
-        make_plan<float2, 8, 32, 32, 256, 3>(),   make_plan<float2, 12, 32, 32, 384, 2>(),
+        make_plan<float2, 8, 16, 16, 128, 6>(),   make_plan<float2, 10, 16, 16, 160, 4>(),
+        make_plan<float2, 12, 16, 16, 192, 4>(),  make_plan<float2, 16, 16, 16, 256, 3>(),
+        make_plan<float2, 10, 16, 32, 160, 4>(),  make_plan<float2, 6, 32, 32, 192, 4>(),
+        make_plan<float2, 8, 32, 32, 256, 3>(),   make_plan<float2, 10, 32, 32, 320, 2>(),
+        make_plan<float2, 12, 32, 32, 384, 2>(),
     };
     return fp32 ? v32 : v64;
 }

@@ -195,7 +195,7 @@ def test_xcorr_fft_ties_and_unequal_amplitudes(eng):
 
 
 @pytest.mark.parametrize("method", [_capi.XCORR_FFT, _capi.XCORR_FFT32], ids=["fft64", "fft32"])
-@pytest.mark.parametrize("n", [128, 255, 384, 700, 1023, 1200, 1537, 2048, 3000, 3100, 4097, 6000, 6144])
+@pytest.mark.parametrize("n", [128, 255, 384, 700, 1023, 1200, 1280, 1537, 2048, 2500, 3000, 3100, 4097, 5000, 6000, 6144])
 def test_xcorr_fft_every_transform_length(eng, n, method):
     """One window length per transform size (512 ... 12288 points), odd channel and pair counts."""
     rng = np.random.default_rng(n)
