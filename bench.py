@@ -207,10 +207,12 @@ def run_b200(args):
         return t, ms_gather
 
     fp64_peak = eng.fp64_peak_tflops(20000)
+    fp32_peak = eng.fp32_peak_tflops(20000)
     for _ in range(args.warmup):
         step_resident()
     barrier()
     launches0 = eng.launch_count()
+    eng.xcorr_stats(reset=True)
     sampler = ClockSampler(local_rank).start()
     wall0 = time.perf_counter()
     dev_ms, stage = 0.0, {"filter": 0.0, "xcorr": 0.0, "solve": 0.0}
@@ -223,6 +225,8 @@ def run_b200(args):
     wall_ms = (time.perf_counter() - wall0) * 1e3
     clocks = sampler.stop()
     launches = eng.launch_count() - launches0
+    xstats = eng.xcorr_stats()
+    xstats["pair_windows"] = int(sum(int(w) for w in plan.win_count) * plan.npairs * args.steps)
     if dist is not None:
         import torch
         tt = torch.tensor([dev_ms, wall_ms], dtype=torch.float64, device="cuda")
@@ -256,7 +260,7 @@ def run_b200(args):
                "ms_per_step_wall": e_wall / args.steps, "ms_per_step_device": e_ms / args.steps}
     return dict(j=j, plan=plan, world=world, rank=rank, value=value, ms_per_step=ms_per_step, wall_ms=wall_ms,
                 stage={k: v / args.steps for k, v in stage.items()}, clocks=clocks, launches=launches, e2e=e2e,
-                fp64_peak=fp64_peak, e_total=e_total, e_local=e_local, shard=shard, sos=sos, win_len=win_len,
+                fp64_peak=fp64_peak, fp32_peak=fp32_peak, xstats=xstats, e_total=e_total, e_local=e_local, shard=shard, sos=sos, win_len=win_len,
                 win_cnt=win_cnt, g_npts=g_npts, dist=dist, keep=keep)
 
 
@@ -326,38 +330,57 @@ def main():
     lib = _capi.load()
     B, C, P = plan.nbands, plan.nchan, plan.npairs
     T = plan.npts
-    flop, n_fft_bands = 0.0, 0
+    fp32 = args.method in ("auto", "fft32")
+    flop, flop64, n_fft_bands = 0.0, 0.0, 0
     for b in range(B):
         W, N = int(plan.win_count[b]), int(plan.win_len[b])
         L = 0
         if args.method != "direct" and (args.method in ("fft", "fft64", "fft32") or N >= 128):
             L = int(lib.nbls_xcorr_fft_length(N, args.max_lag))
         if L:      # FFT path: ceil(C/2) forward + ceil(P/2) inverse complex FFTs of L points (5 L log2 L each),
-            n_fft_bands += 1       # cross-spectra 2 x 6 flop and arg-max 2 compares per point of the inverse
+            n_fft_bands += 1       # cross-spectra 2 x 6 flop and screening/arg-max 2 compares per point of the inverse
             flop += W * (((C + 1) // 2 + (P + 1) // 2) * 5.0 * L * np.log2(L) + ((P + 1) // 2) * L * 16.0)
+            if fp32:   # exact FP64 evaluation of ~1 candidate lag per pair: N multiply-adds
+                flop64 += W * P * 2.0 * N
         else:      # time-domain path: M^2 multiply-adds per pair, M = N rounded up to 8
-            flop += W * P * 2.0 * (-(-N // 8) * 8.0) ** 2
+            flop64 += W * P * 2.0 * (-(-N // 8) * 8.0) ** 2
     x_ms, f_ms = r["stage"]["xcorr"], r["stage"]["filter"]
-    tfl = flop / (x_ms * 1e-3) / 1e12 if x_ms > 0 else None
+    use32 = fp32 and n_fft_bands > 0
+    work = flop if n_fft_bands > 0 else flop64
+    peak = r["fp32_peak"] if use32 else r["fp64_peak"]
+    tfl = work / (x_ms * 1e-3) / 1e12 if x_ms > 0 else None
     filt_bytes = 8.0 * C * T * (1 + 3 * B)
     fgb = filt_bytes / (f_ms * 1e-3) / 1e9 if f_ms > 0 else None
-    kern = ("xf_pair_kernel + xf_spectra_kernel (FP64 FFT cross-correlation)" if n_fft_bands == B else
-            "xcorr_direct_kernel" if n_fft_bands == 0 else "xcorr (FFT and time-domain bands)")
+    if n_fft_bands == 0:
+        kern = "xcorr_direct_kernel"
+    elif use32:
+        kern = "xf_pair_kernel + xf_spectra_kernel (FP32 screening FFTs) + xf_verify_kernel (exact FP64 candidates)"
+    else:
+        kern = "xf_pair_kernel + xf_spectra_kernel (FP64 FFT cross-correlation)"
+    if n_fft_bands not in (0, B):
+        kern += " + xcorr_direct_kernel on the short-window bands"
     line = {"metric": "NBLS band-window estimates/sec", "value": r["value"], "unit": "estimates/s",
             "n_gpus": r["world"], "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": config_block(j, r["world"], args, {"estimates_per_step": r["e_total"]}),
             "clocks": r["clocks"], "gpu_launches": int(r["launches"]), "e2e": r["e2e"],
             "stage_ms": r["stage"], "wall_ms_per_step": r["wall_ms"] / args.steps,
-            "roofline": {"kernel": kern, "bound": "fp64", "achieved": tfl, "peak": r["fp64_peak"],
-                         "unit": "TFLOP/s", "frac": (tfl / r["fp64_peak"]) if tfl else None, "traffic": None,
-                         "peak_source": "DFMA microbenchmark run in this process, 2 flop per FMA (MEASURED_PEAKS.json has no "
-                                        "FP64 entry); FFT butterflies are mostly unfused adds, so 0.5 is the ceiling of this "
-                                        "fraction - see DESIGN.md and profiles/ for the FP64-pipe utilisation from ncu",
-                         "algorithmic_flop_per_step": flop},
+            "roofline": {"kernel": kern, "bound": "fp32" if use32 else "fp64", "achieved": tfl, "peak": peak,
+                         "unit": "TFLOP/s", "frac": (tfl / peak) if tfl else None, "traffic": None,
+                         "peak_source": ("FP32" if use32 else "FP64") + " FMA microbenchmark run in this process, 2 flop per "
+                                        "FMA (MEASURED_PEAKS.json has no such entry; the path is neither HBM- nor tensor-"
+                                        "bound).  FFT butterflies are mostly unfused adds, so 0.5 is the ceiling of this "
+                                        "fraction; ncu (profiles/) gives the issue-slot utilisation of the pair kernel",
+                         "algorithmic_flop_per_step": work, "fp64_verify_flop_per_step": flop64 if use32 else None,
+                         "fp64_peak": r["fp64_peak"], "fp32_peak": r["fp32_peak"]},
             "roofline_filter": {"kernel": "biquad_chunk_kernel x6 + carry x2", "bound": "hbm", "achieved": fgb,
                                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (fgb / peaks["hbm_gbs"]) if fgb else None,
                                 "peak_source": peak_src, "algorithmic_bytes": filt_bytes, "traffic": None}}
+    try:
+        st = r["xstats"]
+        line["xcorr_stats"] = st
+    except KeyError:
+        pass
     if not args.no_cpu:
         v, est, dt = cpu_port_rate(j, args.cpu_sample_min, ncores)
         line["cpu_baseline"] = {"value": v, "unit": "estimates/s", "cores": ncores, "kind": "port",

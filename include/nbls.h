@@ -198,6 +198,8 @@ int64_t nbls_launch_count(nbls_ctx* ctx);
 /* Register-resident DFMA throughput microbenchmark: returns FP64 TFLOP/s (2 flop per FMA)
  * measured over `iters` dependent-chain iterations on every SM. */
 int nbls_measure_fp64_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
+/* The same with FP32 FMAs (roofline denominator of the FP32 screening FFTs). */
+int nbls_measure_fp32_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
 
 #ifdef __cplusplus
 }

@@ -85,6 +85,7 @@ EXPORTS = {
     "nbls_last_timings": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int32]),
     "nbls_launch_count": (C.c_int64, [C.c_void_p]),
     "nbls_measure_fp64_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
+    "nbls_measure_fp32_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
 }
 
 _lib = None

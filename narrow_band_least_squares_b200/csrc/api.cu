@@ -91,11 +91,12 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
     return NBLS_OK;
 }
 
-// ---- FP64 FMA peak microbenchmark ---------------------------------------------------------
-__global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters, double seed) {
-    double a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
-           a7 = a0 + 7;
-    const double m = 0.999999, c = 1e-9;
+// ---- FMA peak microbenchmarks (FP64 and FP32) ---------------------------------------------
+template <class F>
+__global__ void __launch_bounds__(256) fma_peak_kernel(F* out, int iters, F seed) {
+    F a0 = seed + threadIdx.x, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6,
+      a7 = a0 + 7;
+    const F m = (F)0.999999, c = (F)1e-9;
     for (int i = 0; i < iters; ++i) {
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
@@ -106,8 +107,9 @@ __global__ void __launch_bounds__(256) dfma_peak_kernel(double* out, int iters, 
     out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
-int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops) {
-    NBLS_REQUIRE(tflops && iters > 0, "nbls_measure_fp64_peak: bad argument");
+template <class F>
+static int fma_peak(nbls_ctx* ctx, int iters, double* tflops) {
+    NBLS_REQUIRE(tflops && iters > 0, "nbls_measure_fma_peak: bad argument");
     const int blocks = ctx->sm_count * 8, threads = 256;
     NBLS_CHECK(ensure(ctx, ctx->scratch, (size_t)blocks * threads * sizeof(double)));
     cudaEvent_t e0, e1;
@@ -116,7 +118,7 @@ int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops) {
     double best = 0.0;
     for (int rep = 0; rep < 4; ++rep) {
         NBLS_CUDA(cudaEventRecord(e0, ctx->stream));
-        dfma_peak_kernel<<<blocks, threads, 0, ctx->stream>>>((double*)ctx->scratch.p, iters, 1.0 + rep);
+        fma_peak_kernel<F><<<blocks, threads, 0, ctx->stream>>>((F*)ctx->scratch.p, iters, (F)(1.0 + rep));
         NBLS_CUDA(cudaEventRecord(e1, ctx->stream));
         NBLS_CUDA(cudaEventSynchronize(e1));
         float ms = 0;
@@ -130,6 +132,9 @@ int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops) {
     *tflops = best;
     return NBLS_OK;
 }
+
+int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops) { return fma_peak<double>(ctx, iters, tflops); }
+int fp32_peak_impl(nbls_ctx* ctx, int iters, double* tflops) { return fma_peak<float>(ctx, iters, tflops); }
 
 // ---- whole path ---------------------------------------------------------------------------
 static int record(nbls_ctx* ctx, int which) {
@@ -479,6 +484,12 @@ int nbls_measure_fp64_peak(nbls_ctx* ctx, int32_t iters, double* tflops) {
     NBLS_REQUIRE(ctx, "nbls_measure_fp64_peak: null context");
     NBLS_CUDA(cudaSetDevice(ctx->device));
     return fp64_peak_impl(ctx, iters, tflops);
+}
+
+int nbls_measure_fp32_peak(nbls_ctx* ctx, int32_t iters, double* tflops) {
+    NBLS_REQUIRE(ctx, "nbls_measure_fp32_peak: null context");
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    return fp32_peak_impl(ctx, iters, tflops);
 }
 
 }  // extern "C"

@@ -78,6 +78,7 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
 int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_t* lag,
                const double* cmax, const nbls_outputs* out);
 int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
+int fp32_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
 int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
                       int max_lag, int32_t* lag, double* cmax, const int* list, const int* count, int grid_cap);
 int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,

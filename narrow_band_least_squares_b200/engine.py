@@ -225,6 +225,11 @@ class Engine:
         check(self.lib.nbls_measure_fp64_peak(self.ctx, int(iters), C.byref(v)))
         return v.value
 
+    def fp32_peak_tflops(self, iters=20000):
+        v = C.c_double()
+        check(self.lib.nbls_measure_fp32_peak(self.ctx, int(iters), C.byref(v)))
+        return v.value
+
     def xcorr_stats(self, reset=False):
         """Diagnostics of the FP32-screen cross-correlation (nbls_xcorr_stats): candidates verified exactly, items the
         time-domain kernel settled, largest |FP32 screen maximum - exact maximum| seen."""

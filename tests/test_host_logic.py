@@ -47,7 +47,8 @@ def test_fft_length_table():
     lib = _capi.load()
     assert lib.nbls_xcorr_fft_length(3000, -1) == 6144        # N + (N-1) = 5999 -> 6 * 1024
     assert lib.nbls_xcorr_fft_length(6000, -1) == 12288
-    assert lib.nbls_xcorr_fft_length(1200, -1) == 3072
+    assert lib.nbls_xcorr_fft_length(1200, -1) == 2560        # 2399 -> 5 * 512
+    assert lib.nbls_xcorr_fft_length(5000, -1) == 10240       # 9999 -> 5 * 2048
     assert lib.nbls_xcorr_fft_length(3000, 200) == 4096       # restricted lag: N + 200 points suffice
     assert lib.nbls_xcorr_fft_length(6145, -1) == 0           # beyond one SM's shared memory: time-domain kernel
     assert lib.nbls_xcorr_fft_length(0, -1) == 0
