@@ -63,7 +63,7 @@ typedef struct nbls_filter_desc {
                               pass (cheby1 branch, helpers.py:131-137) */
     int32_t exact_scan;    /* 1: chunk end-states from whole chunks (exact linear scan);
                               0: from the last K_b samples only, K_b = decay length of band b
-                              to 2^-80 (contribution below FP64 rounding) */
+                              to 2^-64 (contribution below FP64 rounding) */
     int32_t chunk_len;     /* scan chunk length in samples (multiple of 16); 0 = auto */
     int32_t reserved0;
     int64_t taper_len;     /* wlen of obspy Trace.taper(0.01) (helpers.py:139); 0 = none */

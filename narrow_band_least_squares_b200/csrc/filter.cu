@@ -68,7 +68,7 @@ __device__ __forceinline__ void cp_async_wait() {
 
 // One warp, 32 consecutive chunks of one (band, channel).  EDGE = false is the interior fast path: every chunk of
 // the warp is whole and no sample lies in the taper zones, so loads and stores carry no bounds or taper logic.
-template <int S, bool REV, bool EDGE, bool STATE_ONLY>
+template <int S, bool REV, bool EDGE, bool STATE_ONLY, bool FUSED>
 __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, int band, int chan, int64_t chunk0,
                                             int lane) {
     const int ntiles = a.L / FT_TILE;
@@ -149,9 +149,11 @@ __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, i
             double x = v[j];
 #pragma unroll
             for (int s = 0; s < S; ++s) {
-                if constexpr (STATE_ONLY) {
+                if constexpr (STATE_ONLY || FUSED) {
                     // phase 1 only feeds the chunk-state scan, whose reassociation already differs from the
-                    // sequential order by rounding: fused multiply-adds halve its FP64 instruction count
+                    // sequential order by rounding: fused multiply-adds halve its FP64 instruction count.  The same
+                    // holds for phase 3 of a multi-chunk run (its start states come from that scan); a single-chunk
+                    // run keeps scipy's unfused order below and stays bit-identical to sosfilt
                     const double y = fma(b0[s], x, z0[s]);
                     z0[s] = fma(b1[s], x, fma(-a1[s], y, z1[s]));
                     z1[s] = fma(b2[s], x, -(a2[s] * y));
@@ -221,11 +223,13 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
     if (a.out && a.taper_len > 0)
         edge = edge || (a.g0 + s_lo < a.taper_len) || (a.g0 + s_hi > a.G - a.taper_len);
     if (!a.out) {     // phase 1: chunk end states only
-        if (edge) biquad_warp<S, REV, true, true>(a, ring, band, chan, chunk0, lane);
-        else biquad_warp<S, REV, false, true>(a, ring, band, chan, chunk0, lane);
+        if (edge) biquad_warp<S, REV, true, true, true>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, false, true, true>(a, ring, band, chan, chunk0, lane);
+    } else if (a.nchunks > 1) {
+        if (edge) biquad_warp<S, REV, true, false, true>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, false, false, true>(a, ring, band, chan, chunk0, lane);
     } else {
-        if (edge) biquad_warp<S, REV, true, false>(a, ring, band, chan, chunk0, lane);
-        else biquad_warp<S, REV, false, false>(a, ring, band, chan, chunk0, lane);
+        biquad_warp<S, REV, true, false, false>(a, ring, band, chan, chunk0, lane);
     }
 }
 
@@ -369,7 +373,7 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         if (!d->exact_scan) {
             const double r = max_pole_radius(sb, S);
             if (r > 0.0 && r < 1.0) {
-                const double K = ceil(80.0 * M_LN2 / -log(r));
+                const double K = ceil(64.0 * M_LN2 / -log(r));
                 if (K < (double)L) pt = (int)std::min<double>(ntiles, ceil(K / FT_TILE));
             } else if (r == 0.0) {
                 pt = std::min(ntiles, 2 * S / FT_TILE + 1);   // FIR: state forgets after 2 samples/section
