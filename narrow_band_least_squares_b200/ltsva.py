@@ -4,7 +4,7 @@ Mirrors lts_array/lts_array/ltsva.py:9-54 and the estimator protocol of
 lts_array/lts_array/classes/{lts_data_class.py:15-80, lts_classes.py:799-1036}:
 ``DataBin`` (window grid, tvec, co-array), ``correlate`` (K2), ``solve`` (K3).
 The slowness-ellipse confidence intervals (lts_classes.py:347-640, :715-759, :938-968) are not on
-the narrow-band path; ``conf_int_vel`` / ``conf_int_baz`` are returned as NaN.
+the narrow-band path; ``conf_int_vel`` / ``conf_int_baz`` come from ``uncertainty.py``.
 """
 from __future__ import annotations
 
@@ -101,6 +101,10 @@ class LsBeam:
         self.time_delay_mad = out["mad"]
         self.lts_vel, self.lts_baz, self.sigma_tau = out["vel"], out["baz"], out["sigma_tau"]
         self.slowness = out["slowness"].T
+        # slowness-ellipse uncertainties (lts_classes.py:715-759, :938-968): one vectorised pass over the windows
+        from .uncertainty import slowness_ellipse_ci
+        self.conf_int_vel, self.conf_int_baz = slowness_ellipse_ci(
+            out["slowness"], self.sigma_tau, self.xij, out.get("weights") if alpha != 1.0 else None, self.p)
         return out
 
 

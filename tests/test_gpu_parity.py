@@ -153,7 +153,15 @@ def test_ltsva_surface_and_restricted_lag(eng):
     assert np.array_equal(t, g["b0_t"])
     keys = [k for k in stdict if k != "size"]
     assert keys == [str(k) for k in g["b0_stdict_keys"]] and stdict["size"] == rec.nchans
-    assert np.all(np.isnan(civ)) and np.all(np.isnan(cib))
+    # slowness-ellipse uncertainties: where the origin lies outside the confidence ellipse (every usable estimate) they
+    # agree with the reference's quartic-root machinery; inside it the reference's numbers are the real parts of
+    # complex roots and this implementation reports inf / 180 deg (uncertainty.py)
+    rv, rb = g["b0_conf_int_vel"], g["b0_conf_int_baz"]
+    m = np.isfinite(rv) & np.isfinite(civ)
+    assert m.sum() >= 0.5 * np.isfinite(rv).sum()
+    assert np.allclose(civ[m], rv[m], rtol=1e-5, atol=0)
+    assert np.allclose(cib[m], rb[m], rtol=0, atol=1e-6)
+    assert np.array_equal(np.isnan(civ), np.isnan(vel))
     # restricted lag search against the oracle's sliced arg-max
     L = 150
     n, hop, starts = orc.window_grid(rec.npts, rec.fs, float(g["winlen_list"][0]), float(g["winover"]))

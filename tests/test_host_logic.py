@@ -205,3 +205,41 @@ def test_gather_results_world2_gloo():
     for rank in (0, 1):
         assert np.array_equal(np.array(got[rank]["vel"]), exp)
         assert np.array(got[rank]["lag"]).shape == (15, 5)
+
+
+@pytest.mark.parametrize("name", ["g1_ols_c4", "g2_lts_c6", "g4_lts_c12", "g5_ols_c5_overlap75", "g6_lts_c6_flip"])
+def test_slowness_ellipse_uncertainties_match_reference(name):
+    """conf_int_vel / conf_int_baz (uncertainty.py) against the values the unmodified reference produced
+    (lts_classes.py:715-759, :938-968) wherever the origin lies outside the confidence ellipse."""
+    import os
+    from narrow_band_least_squares_b200.uncertainty import slowness_ellipse_ci
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", name + ".npz"), allow_pickle=True)
+    alpha, checked = float(g["alpha"]), 0
+    for b in range(int(g["nbands"])):
+        vel, baz, sig = g[f"b{b}_vel"], g[f"b{b}_baz"], g[f"b{b}_sigma_tau"]
+        s = 1.0 / vel
+        slow = np.stack([s * np.sin(np.radians(baz)), s * np.cos(np.radians(baz))], axis=1)
+        w = g[f"b{b}_element_weights"].T if alpha != 1.0 else None
+        civ, cib = slowness_ellipse_ci(slow, sig, g["b0_xij"], w)
+        rv, rb = g[f"b{b}_conf_int_vel"], g[f"b{b}_conf_int_baz"]
+        assert np.array_equal(np.isnan(civ), np.isnan(vel))
+        m = np.isfinite(rv) & np.isfinite(civ)
+        assert np.allclose(civ[m], rv[m], rtol=1e-5, atol=0)
+        assert np.allclose(cib[m], rb[m], rtol=0, atol=1e-6)
+        inside = np.isinf(civ)
+        assert np.all(cib[inside] == 180.0)
+        checked += int(m.sum())
+    assert checked > 10
+
+
+def test_slowness_ellipse_known_geometry():
+    """Circle of radius r centred at distance d on the x axis: distances d -+ r, tangent half-angle asin(r/d)."""
+    from narrow_band_least_squares_b200.uncertainty import slowness_ellipse_ci
+    xij = np.array([[1.0, 0.0], [0.0, 1.0], [-1.0, 0.0], [0.0, -1.0]])      # X^T X = 2 I
+    chi = np.sqrt(-2.0 * np.log(0.1))
+    sig = np.array([0.1, 0.2])
+    r = chi * sig / np.sqrt(2.0)
+    d = 3.0
+    civ, cib = slowness_ellipse_ci(np.array([[d, 0.0], [0.0, d]]), sig, xij)
+    assert np.allclose(civ, 0.5 * np.abs(1.0 / (d - r) - 1.0 / (d + r)), rtol=1e-12)
+    assert np.allclose(cib, np.degrees(np.arcsin(r / d)), rtol=1e-10)
