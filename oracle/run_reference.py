@@ -225,6 +225,66 @@ def run_tables(ref):
     print("tables written")
 
 
+def run_helpers(ref):
+    """Known answers for the host helpers on either side of the path: every band layout
+    of get_freqlist (helpers.py:8-79), get_winlenlist (:83-104), the cheby1 branch of filter_data (:129-137) and
+    the results text file (:161-235)."""
+    import contextlib
+    import io
+    import tempfile
+    ref_helpers = ref[0]
+    from narrow_band_least_squares_b200.synth import plane_wave_record
+    out = {}
+    combos = [(0.5, 5.0, 8), (0.1, 10.0, 5), (1.0, 8.0, 3)]
+    for kind in ("linear", "log", "octave", "2_octave_over", "onethird_octave", "octave_linear"):
+        for ci, (fmin, fmax, nb) in enumerate(combos):
+            try:
+                fl, nbc, fmc = ref_helpers.get_freqlist(fmin, fmax, kind, nb)
+            except ZeroDivisionError:        # octave_linear with no band left for the linear part (helpers.py:73)
+                fl, nbc, fmc = [], -1, np.nan
+            out[f"freq_{kind}_{ci}"] = np.asarray(fl, dtype=np.float64)
+            out[f"freq_{kind}_{ci}_meta"] = np.array([fmin, fmax, nb, nbc, fmc], dtype=np.float64)
+    for ci, (kind, nb, wl, w1, wx) in enumerate([("constant", 8, 30.0, 0, 0), ("adaptive", 20, 0, 60.0, 30.0),
+                                                   ("adaptive", 7, 0, 45.0, 12.0)]):
+        out[f"winlen_{ci}"] = np.asarray(ref_helpers.get_winlenlist(kind, nb, wl, w1, wx), dtype=np.float64)
+        out[f"winlen_{ci}_meta"] = np.array([nb, wl, w1, wx], dtype=np.float64)
+    rec = plane_wave_record(seed=1010, nchans=3, npts=9000, fs=50.0, aperture_km=0.3)
+    st = make_stream(rec)
+    for ci, (fmin, fmax, order, ripple) in enumerate([(1.0, 3.0, 2, 0.01), (0.5, 2.0, 4, 0.5)]):
+        stf, fs, sos = ref_helpers.filter_data(st, "cheby1", fmin, fmax, order, ripple)
+        filt = np.stack([tr.data for tr in stf])
+        out[f"cheby_{ci}_meta"] = np.array([fmin, fmax, order, ripple], dtype=np.float64)
+        out[f"cheby_{ci}_sos"] = sos
+        out[f"cheby_{ci}_head"] = filt[:, :128].copy()
+        out[f"cheby_{ci}_mid"] = filt[:, 4500:4628].copy()
+        out[f"cheby_{ci}_tail"] = filt[:, -128:].copy()
+        out[f"cheby_{ci}_rms"] = np.sqrt(np.mean(filt ** 2, axis=1))
+    out["cheby_seed"] = np.array([1010, 3, 9000, 50.0, 0.3])
+    # results text file written by the reference
+    rng = np.random.default_rng(3)
+    fl = np.array([0.5, 1.0, 2.0, 4.0])
+    ncl = [4, 4, 5]          # read_txtfile sizes its arrays by the LAST band (helpers.py:216)
+    arrs = [rng.random((3, 5)) for _ in range(4)]        # vel, baz, mdccm, t
+    arrs[3] = 19000.0 + np.sort(arrs[3], axis=1)
+    with tempfile.TemporaryDirectory() as d:
+        with contextlib.redirect_stdout(io.StringIO()):
+            ref_helpers.write_txtfile(d + "/", "ref", arrs[0], arrs[1], arrs[2], arrs[3], fl, ncl)
+        out["txt_bytes"] = np.frombuffer(open(d + "/ref.txt", "rb").read(), dtype=np.uint8)
+        back = ref_helpers.read_txtfile(d + "/", "ref")
+    for k, v in zip(("vel", "baz", "mdccm", "t"), arrs):
+        out[f"txt_{k}"] = v
+    out["txt_freqlist"], out["txt_ncl"] = fl, np.asarray(ncl)
+    for k, v in zip(("vel", "baz", "mdccm", "t", "freqlist", "ncl"), back[:6]):
+        v = np.asarray(v, dtype=np.float64).copy()
+        if v.ndim == 2:
+            for ii in range(3):
+                v[ii, ncl[ii]:] = np.nan          # np.empty garbage beyond a band's count
+        out[f"txt_back_{k}"] = v
+    out["txt_back_scalars"] = np.array([back[6], back[7], back[8]], dtype=np.float64)
+    np.savez_compressed(os.path.join(GOLD, "helpers.npz"), **out)
+    print("helpers written")
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default=None)
@@ -234,6 +294,8 @@ def main():
     os.makedirs(GOLD, exist_ok=True)
     if a.only in (None, "tables"):
         run_tables(ref)
+    if a.only in (None, "helpers"):
+        run_helpers(ref)
     for name in CASES:
         if a.only in (None, name):
             run_case(name, ref)

@@ -221,6 +221,25 @@ def test_xcorr_fft_every_transform_length(eng, n, method):
     assert np.array_equal(lag2, ref2)
 
 
+def test_cheby1_branch_matches_reference(eng):
+    """FILTER_TYPE='cheby1' (helpers.py:129-137 of the reference: one causal sosfilt pass, then the 1 % taper) through
+    the package's filter_data on the GPU, against samples the unmodified reference produced (tests/golden/helpers.npz)."""
+    from narrow_band_least_squares_b200 import helpers
+    g = np.load(os.path.join(GOLD, "helpers.npz"), allow_pickle=True)
+    seed, nch, npts, fs, ap = g["cheby_seed"]
+    rec = plane_wave_record(seed=int(seed), nchans=int(nch), npts=int(npts), fs=float(fs), aperture_km=float(ap))
+    for ci in range(2):
+        fmin, fmax, order, ripple = g[f"cheby_{ci}_meta"]
+        stf, fs_out, sos = helpers.filter_data((rec.data, rec.fs, None), "cheby1", float(fmin), float(fmax), int(order),
+                                               float(ripple))
+        filt = stf[0]                      # tuple in -> tuple out (stream.like_stream)
+        assert np.array_equal(np.asarray(sos), g[f"cheby_{ci}_sos"])
+        tol = 1e-12 * float(g[f"cheby_{ci}_rms"].max())
+        assert np.allclose(filt[:, :128], g[f"cheby_{ci}_head"], rtol=0, atol=tol)
+        assert np.allclose(filt[:, 4500:4628], g[f"cheby_{ci}_mid"], rtol=0, atol=tol)
+        assert np.allclose(filt[:, -128:], g[f"cheby_{ci}_tail"], rtol=0, atol=tol)
+
+
 def test_xcorr_fp32_screen_statistics(eng):
     """The FP32 screen hands ~1 candidate per pair-window to the exact FP64 evaluation and its maximum agrees with the
     exact one far inside the candidate band (2e-5): the margin that makes the integer lags FP64-exact."""

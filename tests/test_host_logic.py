@@ -243,3 +243,48 @@ def test_slowness_ellipse_known_geometry():
     civ, cib = slowness_ellipse_ci(np.array([[d, 0.0], [0.0, d]]), sig, xij)
     assert np.allclose(civ, 0.5 * np.abs(1.0 / (d - r) - 1.0 / (d + r)), rtol=1e-12)
     assert np.allclose(cib, np.degrees(np.arcsin(r / d)), rtol=1e-10)
+
+
+def _helpers_golden():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "helpers.npz"), allow_pickle=True)
+
+
+def test_freqlist_every_band_layout_matches_reference():
+    """get_freqlist for 'linear', 'log', 'octave', '2_octave_over', 'onethird_octave', 'octave_linear' against the
+    lists the unmodified reference produced (helpers.py:8-79; fixture written by oracle/run_reference.py)."""
+    g = _helpers_golden()
+    n = 0
+    for kind in ("linear", "log", "octave", "2_octave_over", "onethird_octave", "octave_linear"):
+        for ci in range(3):
+            fmin, fmax, nb, nbc, fmc = g[f"freq_{kind}_{ci}_meta"]
+            if nbc < 0:      # the reference divides by zero (octave_linear without a linear part)
+                with pytest.raises(ZeroDivisionError):
+                    helpers.get_freqlist(float(fmin), float(fmax), kind, int(nb))
+                continue
+            fl, nbands_calc, fmax_calc = helpers.get_freqlist(float(fmin), float(fmax), kind, int(nb))
+            assert np.array_equal(np.asarray(fl, dtype=np.float64), g[f"freq_{kind}_{ci}"]), (kind, ci)
+            assert nbands_calc == int(nbc) and fmax_calc == fmc
+            n += 1
+    assert n >= 15
+
+
+def test_winlenlist_matches_reference():
+    g = _helpers_golden()
+    for ci, kind in enumerate(("constant", "adaptive", "adaptive")):
+        nb, wl, w1, wx = g[f"winlen_{ci}_meta"]
+        got = helpers.get_winlenlist(kind, int(nb), wl, w1, wx)
+        assert np.array_equal(np.asarray(got, dtype=np.float64), g[f"winlen_{ci}"])
+
+
+def test_results_txtfile_is_byte_identical_to_reference(tmp_path):
+    """write_txtfile produces the reference's file byte for byte (helpers.py:161-181); read_txtfile returns what
+    the reference's reader returns (helpers.py:184-235)."""
+    g = _helpers_golden()
+    d = str(tmp_path) + "/"
+    helpers.write_txtfile(d, "mine", g["txt_vel"], g["txt_baz"], g["txt_mdccm"], g["txt_t"], g["txt_freqlist"],
+                          [int(v) for v in g["txt_ncl"]])
+    assert open(d + "mine.txt", "rb").read() == g["txt_bytes"].tobytes()
+    back = helpers.read_txtfile(d, "mine")
+    for k, v in zip(("vel", "baz", "mdccm", "t", "freqlist", "ncl"), back[:6]):
+        assert np.array_equal(np.asarray(v, dtype=np.float64), g[f"txt_back_{k}"], equal_nan=True), k
+    assert np.array_equal(np.array(back[6:9], dtype=np.float64), g["txt_back_scalars"])
