@@ -59,7 +59,12 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.t_mark = index, [], None, None
+
+    def mark(self):
+        """Start of the timed region: only samples read after this count (nvidia-smi is started before the warm-up
+        steps so that its start-up does not stall the first timed step)."""
+        self.t_mark = time.perf_counter()
 
     def start(self):
         try:
@@ -74,7 +79,7 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
 
     def stop(self):
         if self.proc is None:
@@ -85,7 +90,10 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, reasons, pw = [], [], set(), []
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.t_mark is None or t >= self.t_mark]
+        if not rows:                      # timed region shorter than one sampling period: take the last sample
+            rows = [r for _, r in self.rows[-1:]]
+        for r in rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
             except Exception:
@@ -208,12 +216,13 @@ def run_b200(args):
 
     fp64_peak = eng.fp64_peak_tflops(20000)
     fp32_peak = eng.fp32_peak_tflops(20000)
+    sampler = ClockSampler(local_rank).start()
     for _ in range(args.warmup):
         step_resident()
     barrier()
     launches0 = eng.launch_count()
     eng.xcorr_stats(reset=True)
-    sampler = ClockSampler(local_rank).start()
+    sampler.mark()
     wall0 = time.perf_counter()
     dev_ms, stage = 0.0, {"filter": 0.0, "xcorr": 0.0, "solve": 0.0}
     for _ in range(args.steps):

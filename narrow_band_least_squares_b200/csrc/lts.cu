@@ -15,9 +15,11 @@
 // A warp runs one start at a time with its lanes spread over the P pairs; ranking is by counting
 // (rank_p = #{q : |r_q| < |r_p| or tie with q < p}), which yields the h-subset and the objective in
 // one pass and makes every fit a deterministic function of the subset.
+#include <cuda_fp16.h>
 #include <float.h>
 #include <math.h>
 #include <math_constants.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -81,15 +83,110 @@ __device__ __forceinline__ Sums rank_pass(const double* x0, const double* x1, co
     return s;
 }
 
+// The same pass with the h-subset found through FP16 keys (NI = items per lane, P <= 32 NI <= 2016).  Rounding
+// |r| to FP16 is monotone, so with le(p) = #{q : key_q <= key_p} (counted two keys per instruction, exactly, in
+// half2 arithmetic: counts stay below 2048)
+//   le(p) <= h                  =>  rank_p < h            (p is in the subset),
+//   key_p > K*, K* = smallest key with le > h  =>  rank_p >= h   (p is not),
+// and only if the FP16 tie group at K* straddles the boundary (a few per cent of the passes) are its members
+// ranked with the exact FP64 rule.  The subset, and hence the sums, are identical to rank_pass's.
+template <int NI>
+__device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, const double* y, double* absr,
+                                            __half2* key2, int P, int h, double zx, double zy, int lane) {
+    __half* key = reinterpret_cast<__half*>(key2);
+    const unsigned short* keyb = reinterpret_cast<const unsigned short*>(key2);
+    const __half hnan = __ushort_as_half((unsigned short)0x7E00);
+    double v[NI];
+    __half2 kp[NI], cnt[NI];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+        const int p = lane + 32 * i;
+        v[i] = 0.0;
+        kp[i] = __half2half2(hnan);
+        cnt[i] = __float2half2_rn(0.f);
+        if (p < P) {
+            v[i] = fabs(y[p] - (x0[p] * zx + x1[p] * zy));
+            absr[p] = v[i];
+            const __half k = __double2half(v[i]);
+            key[p] = k;
+            kp[i] = __half2half2(k);
+        }
+    }
+    if (lane == 0 && (P & 1)) key[P] = hnan;      // pad to a whole half2: NaN compares false
+    __syncwarp();
+    const int P2 = (P + 1) >> 1;
+    for (int q2 = 0; q2 < P2; ++q2) {
+        const __half2 kq = key2[q2];
+#pragma unroll
+        for (int i = 0; i < NI; ++i) cnt[i] = __hadd2(cnt[i], __hle2(kq, kp[i]));
+    }
+    bool in[NI];
+    int n_in = 0;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+        const int p = lane + 32 * i;
+        const int le = (int)(__low2float(cnt[i]) + __high2float(cnt[i]));
+        in[i] = (p < P) && (le <= h);
+        n_in += __popc(__ballot_sync(0xffffffffu, in[i]));
+    }
+    if (n_in < h) {        // warp-uniform: the tie group at K* straddles the boundary
+        const int need = h - n_in;
+        unsigned kmin = 0xFFFFu;
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int p = lane + 32 * i;
+            if (p < P && !in[i]) kmin = min(kmin, (unsigned)__half_as_ushort(__low2half(kp[i])));
+        }
+        kmin = __reduce_min_sync(0xffffffffu, kmin);
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int p = lane + 32 * i;
+            if (p < P && !in[i] && (unsigned)__half_as_ushort(__low2half(kp[i])) == kmin) {
+                int r = 0;
+                for (int q = 0; q < P; ++q) {
+                    if ((unsigned)keyb[q] == kmin) {
+                        const double u = absr[q];
+                        r += (u < v[i]) || (u == v[i] && q < p);
+                    }
+                }
+                in[i] = r < need;
+            }
+        }
+    }
+    Sums s = {0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+        const int p = lane + 32 * i;
+        if (in[i]) {
+            const double a = x0[p], b = x1[p], t = y[p];
+            s.sxx = fma(a, a, s.sxx); s.sxy = fma(a, b, s.sxy); s.syy = fma(b, b, s.syy);
+            s.sxt = fma(a, t, s.sxt); s.syt = fma(b, t, s.syt);
+            s.obj = fma(v[i], v[i], s.obj);
+        }
+    }
+    __syncwarp();
+    s.sxx = warp_sum(s.sxx); s.sxy = warp_sum(s.sxy); s.syy = warp_sum(s.syy);
+    s.sxt = warp_sum(s.sxt); s.syt = warp_sum(s.syt); s.obj = warp_sum(s.obj);
+    return s;
+}
+
+template <int NI>
+__device__ __forceinline__ Sums rank_any(const double* x0, const double* x1, const double* y, double* absr, __half2* key2,
+                                         int P, int h, double zx, double zy, int lane) {
+    if constexpr (NI == 0) return rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
+    else return rank_pass16<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
+}
+
 // C-steps from (zx, zy) until the objective repeats or `limit` steps (:89-103 / :125-139)
-__device__ __forceinline__ void csteps(const double* x0, const double* x1, const double* y, double* absr, int P, int h,
-                                       int limit, double& zx, double& zy, double& obj, int lane) {
-    Sums s = rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
+template <int NI>
+__device__ __forceinline__ void csteps(const double* x0, const double* x1, const double* y, double* absr, __half2* key2,
+                                       int P, int h, int limit, double& zx, double& zy, double& obj, int lane) {
+    Sums s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
     double prev = 0.0;
     obj = s.obj;
     for (int kk = 0; kk < limit; ++kk) {
         solve2(s, zx, zy);
-        s = rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
+        s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
         obj = s.obj;
         if (kk >= 1 && obj == prev) break;
         prev = obj;
@@ -112,6 +209,7 @@ __device__ __forceinline__ void fit2(const double* x0, const double* x1, const d
     }
 }
 
+template <int NI>
 __global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
     extern __shared__ double sm[];
     const int P = a.P, NS = a.n_starts, NK = a.n_keep;
@@ -119,8 +217,9 @@ __global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
     double* x0 = ys + P;               // [P]
     double* x1 = x0 + P;               // [P]
     double* tau = x1 + P;              // [P] seconds
-    double* scratch = tau + P;         // [LTS_WARPS][P]
-    double* sobj = scratch + (size_t)LTS_WARPS * P;   // [NS]
+    const int KW = (P + 5) / 4;        // doubles holding P+1 FP16 keys
+    double* scratch = tau + P;         // [LTS_WARPS][P + KW]: |r| and its FP16 keys, per warp
+    double* sobj = scratch + (size_t)LTS_WARPS * (P + KW);   // [NS]
     double* szx = sobj + NS;           // [NS]
     double* szy = szx + NS;            // [NS]
     double* cobj = szy + NS;           // [NK]
@@ -130,7 +229,8 @@ __global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
     __shared__ int sh_skip, sh_ncand;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    double* absr = scratch + (size_t)warp * P;
+    double* absr = scratch + (size_t)warp * (P + KW);
+    __half2* key2 = reinterpret_cast<__half2*>(absr + P);
 
     for (int64_t e = blockIdx.x; e < a.nwin; e += gridDim.x) {
         const int32_t* lag = a.lag + e * P;
@@ -170,7 +270,7 @@ __global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
         for (int s = warp; s < NS; s += LTS_WARPS) {
             double zx, zy, obj;
             fit2(x0, x1, ys, a.subsets[2 * s], a.subsets[2 * s + 1], zx, zy);
-            csteps(x0, x1, ys, absr, P, a.h, a.csteps1, zx, zy, obj, lane);
+            csteps<NI>(x0, x1, ys, absr, key2, P, a.h, a.csteps1, zx, zy, obj, lane);
             if (lane == 0) { sobj[s] = obj; szx[s] = zx; szy[s] = zy; }
         }
         __syncthreads();
@@ -198,7 +298,7 @@ __global__ void __launch_bounds__(LTS_WARPS * 32) lts_kernel(LtsArgs a) {
                 fit2(x0, x1, ys, a.subsets[2 * s], a.subsets[2 * s + 1], zx, zy);
             }
             ok = isfinite(zx);
-            if (ok) csteps(x0, x1, ys, absr, P, a.h, a.csteps2, zx, zy, obj, lane);
+            if (ok) csteps<NI>(x0, x1, ys, absr, key2, P, a.h, a.csteps2, zx, zy, obj, lane);
             __syncwarp();
             if (lane == 0) { cobj[c] = ok ? obj : qnan(); czx[c] = zx; czy[c] = zy; }
         }
@@ -318,11 +418,19 @@ int lts_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_
     a.lag = lag; a.cmax = cmax; a.xij = dgeom; a.subsets = dsub; a.rew_cons = drew;
     a.mdccm = out->mdccm; a.mad = out->mad; a.vel = out->vel; a.baz = out->baz; a.sig = out->sigma_tau;
     a.slow = out->slowness; a.weights = out->weights;
-    const size_t smem = ((size_t)(4 + LTS_WARPS) * P + 3 * (size_t)s->n_starts + 3 * (size_t)s->n_keep) * sizeof(double);
+    const int KW = (P + 5) / 4;
+    const size_t smem = ((size_t)4 * P + (size_t)LTS_WARPS * (P + KW) + 3 * (size_t)s->n_starts + 3 * (size_t)s->n_keep) *
+                        sizeof(double);
     NBLS_REQUIRE(smem <= ctx->smem_optin, "nbls_solve: LTS working set of %zu B exceeds shared memory", smem);
-    NBLS_CUDA(cudaFuncSetAttribute(lts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // items per lane of the FP16-key ranking; 0 = generic FP64 counting (P > 320)
+    typedef void (*lts_fn)(LtsArgs);
+    static const lts_fn table[11] = {lts_kernel<0>, lts_kernel<1>, lts_kernel<2>, lts_kernel<3>, lts_kernel<4>, lts_kernel<5>,
+                                     lts_kernel<6>, lts_kernel<7>, lts_kernel<8>, lts_kernel<9>, lts_kernel<10>};
+    const int ni = (P + 31) / 32;
+    const lts_fn fn = table[(ni <= 10 && !getenv("NBLS_LTS_FP64_RANK")) ? ni : 0];
+    NBLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (int)std::min<int64_t>(nwin, (int64_t)ctx->sm_count * 32);
-    lts_kernel<<<grid, LTS_WARPS * 32, smem, ctx->stream>>>(a);
+    fn<<<grid, LTS_WARPS * 32, smem, ctx->stream>>>(a);
     NBLS_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return NBLS_OK;
