@@ -305,3 +305,35 @@ def test_time_sharded_run_equals_unsharded(eng, alpha):
         assert np.allclose(merge_band_major(parts[k], counts), getattr(ref, k), rtol=1e-9, atol=1e-12, equal_nan=True), k
     d = np.abs(((merge_band_major(parts["baz"], counts) - ref.baz + 180.0) % 360.0) - 180.0)
     assert np.nanmax(d, initial=0.0) < 1e-6
+
+
+def test_c3_sized_methods_agree_end_to_end(eng):
+    """BASELINE config 3 at its real array and band sizes (25 elements = 300 pairs, 20 log bands, windows 60 -> 30 s, i.e.
+    transforms of 12288, 10240, 8192 and 6144 points) on a 15-minute record: the default path (FP32 screen + exact
+    FP64 candidates), the FP64 FFT path and the exact time-domain kernel give the same integer lags, cmax to 1e-12 and
+    the same estimates; the screen's error stays far inside its candidate band and nothing needs the fallback."""
+    from narrow_band_least_squares_b200.configs import config_plan
+    from narrow_band_least_squares_b200.engine import Results
+    from narrow_band_least_squares_b200.synth import config_record
+    rec = config_record("c3", hours=0.25)
+    out = {}
+    for name, method in (("fft32", _capi.XCORR_FFT32), ("fft64", _capi.XCORR_FFT), ("direct", _capi.XCORR_DIRECT)):
+        plan = config_plan("c3", rec.npts, rec.rij, method=method)
+        if name == "fft32":
+            eng.xcorr_stats(reset=True)
+        res = eng.run(plan, rec.data, Results(plan, pinned=False))
+        if name == "fft32":
+            st = eng.xcorr_stats(reset=True)
+        out[name] = {k: np.array(getattr(res, k)[:plan.nwin]) for k in ("lag", "cmax", "vel", "baz", "mdccm", "sigma_tau")}
+        nwin, npairs = plan.nwin, plan.npairs
+    assert npairs == 300 and nwin > 600
+    for other in ("fft64", "direct"):
+        assert np.array_equal(out["fft32"]["lag"], out[other]["lag"]), other
+        assert np.allclose(out["fft32"]["cmax"], out[other]["cmax"], rtol=0, atol=1e-12, equal_nan=True), other
+        for k in ("vel", "baz", "mdccm", "sigma_tau"):
+            assert np.allclose(out["fft32"][k], out[other][k], rtol=1e-9, atol=1e-12, equal_nan=True), (other, k)
+    assert st["time_domain"] == 0 and st["max_screen_err"] < 5e-6, st
+    assert nwin * npairs <= st["verified"] <= 1.2 * nwin * npairs, st
+    v = out["fft32"]["vel"]
+    good = np.isfinite(v)
+    assert good.mean() > 0.5 and abs(np.median(v[good]) - 0.34) < 0.02      # the synthetic plane wave is recovered
