@@ -654,7 +654,11 @@ __global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
                 lo = max(lo, nk);
                 hi = min(hi, N + nk);
             }
+            // whole blocks of 256 samples for the unchecked part, so that none of the three calls leaves a ragged tail
+            // inside the slice (the checked path costs more per sample but the edges are short)
+            lo = a + (lo - a + 255) / 256 * 256;
             lo = min(lo, b);
+            hi = hi < b ? lo + max(hi - lo, 0) / 256 * 256 : b;
             hi = max(hi, lo);
             double acc[IB];
 #pragma unroll
@@ -662,14 +666,32 @@ __global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
             if (a < lo) verify_slice<IB, true>(xj, xs, off, k, a, lo, N, lane, acc);
             verify_slice<IB, false>(xj, xs, off, k, lo, hi, N, lane, acc);
             if (hi < b) verify_slice<IB, true>(xj, xs, off, k, hi, b, N, lane, acc);
+            double* dst = sp + (size_t)(j - i_base - 1) * IB * XV_SL + sl;
+            if constexpr (IB == 4) {
+                // packed butterfly: after the exchange over 16 a lane carries two of the four sums, after 8 one; the
+                // totals end in lanes 0, 8, 16, 24 (ii = 0, 1, 2, 3) in a fixed order: 12 shuffles instead of 40
+                const bool up16 = (lane & 16) != 0, up8 = (lane & 8) != 0;
+                double s0 = up16 ? acc[0] : acc[2], s1 = up16 ? acc[1] : acc[3];     // what this lane gives away
+                double k0 = up16 ? acc[2] : acc[0], k1 = up16 ? acc[3] : acc[1];     // what it keeps
+                k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+                k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+                const double g = up8 ? k0 : k1;
+                double t = up8 ? k1 : k0;
+                t += __shfl_xor_sync(0xffffffffu, g, 8);
+                t += __shfl_xor_sync(0xffffffffu, t, 4);
+                t += __shfl_xor_sync(0xffffffffu, t, 2);
+                t += __shfl_xor_sync(0xffffffffu, t, 1);
+                if ((lane & 7) == 0) dst[((lane >> 4) * 2 + ((lane >> 3) & 1)) * XV_SL] = t;
+            } else {
 #pragma unroll
-            for (int ii = 0; ii < IB; ++ii) {
+                for (int ii = 0; ii < IB; ++ii) {
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) acc[ii] += __shfl_xor_sync(0xffffffffu, acc[ii], o);
-            }
-            if (lane == 0) {
+                    for (int o = 16; o > 0; o >>= 1) acc[ii] += __shfl_xor_sync(0xffffffffu, acc[ii], o);
+                }
+                if (lane == 0) {
 #pragma unroll
-                for (int ii = 0; ii < IB; ++ii) sp[((j - i_base - 1) * IB + ii) * XV_SL + sl] = acc[ii];
+                    for (int ii = 0; ii < IB; ++ii) dst[ii * XV_SL] = acc[ii];
+                }
             }
         }
     }
