@@ -44,7 +44,7 @@ extern "C" {
 #define NBLS_MAX_SECTIONS 8
 #define NBLS_MAX_BANDS 256
 
-#define NBLS_XCORR_AUTO 0
+#define NBLS_XCORR_AUTO 0   /* FFT32 with the two-stage lag search where it applies (see below), else DIRECT */
 #define NBLS_XCORR_DIRECT 1 /* time-domain FP64 contraction over the circularly padded window */
 #define NBLS_XCORR_FFT 2    /* shared-memory FP64 FFT + exact re-evaluation of near-tied lags */
 #define NBLS_XCORR_FFT32 3  /* FP32 FFT screens the lags, every candidate within 2e-5 of the FP32 maximum is
@@ -110,6 +110,13 @@ int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag);
  * (normalised correlation units; the screen's candidate band is 2e-5).  Synchronises.  Any pointer may be NULL. */
 int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain, double* max_screen_err,
                      int32_t reset);
+
+/* Two-stage lag search of NBLS_XCORR_AUTO (all 2N-1 lags requested, FP32 screen): stage A searches |lag| <= k0 with a
+ * shorter transform and proves for every pair-window - Cauchy-Schwarz over the partial energies of the two windows - that no
+ * lag beyond k0 can reach the maximum found; windows without a proof are redone over all lags, so the result is the arg-max
+ * over all 2N-1 lags either way.  A band where most windows needed the second stage switches the next three bands to the
+ * single-stage search.  Returns the windows searched in two stages and those redone since creation / the last reset. */
+int nbls_xcorr_two_stage_stats(nbls_ctx* ctx, int64_t* n_windows, int64_t* n_redone, int32_t reset);
 
 /* ---- K3: per-window statistics and slowness solve ---------------------------------- */
 typedef struct nbls_solve_desc {

@@ -76,6 +76,7 @@ EXPORTS = {
                              C.c_void_p, C.c_void_p]),
     "nbls_xcorr_fft_length": (C.c_int, [C.c_int32, C.c_int32]),
     "nbls_xcorr_stats": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p, c_double_p, C.c_int32]),
+    "nbls_xcorr_two_stage_stats": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p, C.c_int32]),
     "nbls_solve": (C.c_int, [C.c_void_p, C.POINTER(SolveDesc), C.c_int64, C.c_void_p, C.c_void_p,
                              C.POINTER(Outputs)]),
     "nbls_run_device": (C.c_int, [C.c_void_p, C.POINTER(Job), C.c_void_p, C.c_int32, C.c_int64, C.c_int64,

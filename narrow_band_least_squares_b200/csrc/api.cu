@@ -82,7 +82,7 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
         const double* yb = y + (int64_t)b * ystride_band;
         if (method != NBLS_XCORR_DIRECT)
             NBLS_CHECK(xcorr_fft_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb,
-                                      method == NBLS_XCORR_FFT32));
+                                      method == NBLS_XCORR_FFT32, w->method == NBLS_XCORR_AUTO));
         else
             NBLS_CHECK(xcorr_direct_band(ctx, yb, ldy, C, N, w->win_hop[b], w->win_first[b], W, w->max_lag, lb, cb,
                                          nullptr, nullptr, 0));
@@ -263,7 +263,7 @@ int nbls_destroy(nbls_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->coef, &ctx->state, &ctx->carry, &ctx->taper, &ctx->filt, &ctx->geom, &ctx->lts_tab,
                       &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch, &ctx->spec,
-                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat};
+                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat, &ctx->wfail};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& kv : ctx->fft_tw)
@@ -382,6 +382,14 @@ int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain,
         memcpy(&f, &bits, sizeof(f));
         *max_screen_err = (double)f;
     }
+    return NBLS_OK;
+}
+
+int nbls_xcorr_two_stage_stats(nbls_ctx* ctx, int64_t* n_windows, int64_t* n_redone, int32_t reset) {
+    NBLS_REQUIRE(ctx, "nbls_xcorr_two_stage_stats: null context");
+    if (n_windows) *n_windows = ctx->ts_windows;
+    if (n_redone) *n_redone = ctx->ts_redone;
+    if (reset) { ctx->ts_windows = 0; ctx->ts_redone = 0; ctx->ts_skip = 0; }
     return NBLS_OK;
 }
 

@@ -60,6 +60,9 @@ struct nbls_ctx {
     nbls::DevBuf coef, state, carry, taper, filt, geom, lts_tab, xin, res, lagbuf, cmaxbuf, wbuf, scratch;
     nbls::DevBuf spec, energy, flags;       // FFT cross-correlation workspace
     nbls::DevBuf cand, sval, xstat;         // FP32 screen: candidate lags, screen maxima; xcorr statistics
+    nbls::DevBuf wfail;                     // two-stage lag search: failed-window flags and list
+    int ts_skip = 0;                        // bands left to the single-stage search after a band that mostly failed
+    int64_t ts_windows = 0, ts_redone = 0;  // two-stage statistics: windows searched / redone over all lags
     std::map<int, void*> fft_tw;            // twiddle tables by transform length (device)
     cudaEvent_t ev[nbls::EV_COUNT] = {};
     bool ev_valid = false;
@@ -82,7 +85,7 @@ int fp32_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
 int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
                       int max_lag, int32_t* lag, double* cmax, const int* list, const int* count, int grid_cap);
 int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                   int max_lag, int32_t* lag, double* cmax, bool fp32);
+                   int max_lag, int32_t* lag, double* cmax, bool fp32, bool two_stage);
 // transform length the FFT path would use for a window of N samples and lag bound, 0 if unsupported
 int xcorr_fft_length(int N, int max_lag);
 

@@ -32,6 +32,7 @@
 #include <limits.h>
 #include <math.h>
 #include <math_constants.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -69,7 +70,17 @@ struct XfArgs {
     float* sval;          // FP32 screen: [wn*P] the FP32 maximum (normalised)
     unsigned long long* stat;   // [0] candidates verified, [1] items sent to the time-domain kernel,
                                 // [2] max |FP32 max - exact max| as float bits
+    // two-stage lag search (FP32 screen only).  Stage A searches |lag| <= k0 with a shorter transform and proves per
+    // pair-window, by Cauchy-Schwarz over partial energies, that no lag beyond k0 can reach the maximum found; the
+    // windows where the proof fails for some pair are listed (wfail) and redone over all lags (stage B, wlist).
+    int k0;               // stage A: lag bound of the search (>= 0); otherwise -1
+    int lag_dead;         // lag written for a zero-energy pair: -(N-1) or -max_lag of the request
+    double* part;         // stage A: [wn][C][2] = sum of x^2 over n < N-k0-1 (head) and over n > k0 (tail)
+    int* wfail;           // stage A: [wn] set to 1 when some pair of the window fails the proof
+    const int* wlist;     // stage B: band-level window index of batch slot wl; nullptr = w0 + wl
 };
+
+__device__ __forceinline__ int win_index(const XfArgs& g, int wl) { return g.wlist ? g.wlist[wl] : g.w0 + wl; }
 
 template <int R1_, int R2_, int R3_>
 struct Shape {
@@ -138,16 +149,43 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     const int wl = blockIdx.x / ncp, cp = blockIdx.x - wl * ncp;
     const int ca = 2 * cp, cb = 2 * cp + 1;
     const bool has_b = cb < g.C;
-    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+    const int64_t t0 = g.first + (int64_t)win_index(g, wl) * g.hop;
     const double* xa = g.y + (int64_t)ca * g.ldy + t0;
     const double* xb = g.y + (int64_t)(has_b ? cb : ca) * g.ldy + t0;
 
     // energies (same accumulation as the time-domain kernel: strided fma, then tree)
     double ea = 0.0, eb = 0.0;
-    for (int n = tid; n < g.N; n += T) {
-        const double va = xa[n], vb = xb[n];
-        ea = fma(va, va, ea);
-        eb = fma(vb, vb, eb);
+    if (g.k0 >= 0) {
+        // stage A of the two-stage search: also the head (n < N-k0-1) and tail (n > k0) energies of both channels
+        __shared__ double redp[4][T / 32];
+        const int nh = g.N - g.k0 - 1, nt = g.k0;
+        double ha = 0.0, ta = 0.0, hb = 0.0, tb = 0.0;
+        for (int n = tid; n < g.N; n += T) {
+            const double va = xa[n], vb = xb[n];
+            const double qa = va * va, qb = vb * vb;
+            ea = fma(va, va, ea);           // the window energies keep the accumulation of every other path
+            eb = fma(vb, vb, eb);
+            if (n < nh) { ha += qa; hb += qb; }
+            if (n > nt) { ta += qa; tb += qb; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            ha += __shfl_xor_sync(0xffffffffu, ha, o); ta += __shfl_xor_sync(0xffffffffu, ta, o);
+            hb += __shfl_xor_sync(0xffffffffu, hb, o); tb += __shfl_xor_sync(0xffffffffu, tb, o);
+        }
+        if (lane == 0) { redp[0][warp] = ha; redp[1][warp] = ta; redp[2][warp] = hb; redp[3][warp] = tb; }
+        __syncthreads();
+        if (tid < 4 && (tid < 2 || has_b)) {
+            double v = 0.0;
+            for (int i = 0; i < T / 32; ++i) v += redp[tid][i];
+            g.part[((int64_t)wl * g.C + (tid < 2 ? ca : cb)) * 2 + (tid & 1)] = v;
+        }
+    } else {
+        for (int n = tid; n < g.N; n += T) {
+            const double va = xa[n], vb = xb[n];
+            ea = fma(va, va, ea);
+            eb = fma(vb, vb, eb);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -448,14 +486,14 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
             const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
             const double den = sqrt(Ei * Ej);
-            const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+            const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
             const int64_t loc = (int64_t)wl * g.P + p;
             const int cnt = scnt[tid];
             int32_t* cd = g.cand + loc * XF_KC;
             bool give = false;
             if (!(den > 0.0)) {
                 // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched
-                g.lag[item] = -lag_max;
+                g.lag[item] = g.lag_dead;
                 if (g.cmax) g.cmax[item] = __longlong_as_double(0x7ff8000000000000LL);
             } else if (!isfinite(den) || cnt < 1 || cnt > XF_KC) {
                 // non-finite data, or too many near-tied lags: the time-domain kernel evaluates every lag
@@ -527,10 +565,10 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
         const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
         const double den = sqrt(Ei * Ej);
-        const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+        const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
         if (!(den > 0.0)) {
             // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched
-            g.lag[item] = -lag_max;
+            g.lag[item] = g.lag_dead;
             if (g.cmax) g.cmax[item] = __longlong_as_double(0x7ff8000000000000LL);
         } else {
             g.lag[item] = b.l1 == INT_MAX ? -lag_max : b.l1;
@@ -615,7 +653,7 @@ __global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
     const int nib = (g.C - 1 + IB - 1) / IB;
     const int wl = blockIdx.x / nib, ib = blockIdx.x - wl * nib;
     const int i_base = ib * IB;
-    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+    const int64_t t0 = g.first + (int64_t)win_index(g, wl) * g.hop;
     if (tid == 0) ecount = 0;
     const int njj = g.C - 1 - i_base;                    // channels j = i_base+1 .. C-1
     for (int e = tid; e < njj * IB; e += XV_WARPS * 32) {
@@ -746,9 +784,17 @@ __global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
         }
         const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
         const double c = best / sqrt(Ei * Ej);
-        const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+        const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
         g.lag[item] = bl;
         if (g.cmax) g.cmax[item] = c;
+        if (g.k0 >= 0) {
+            // |c[k]| <= sqrt(sum x_i^2 * sum x_j^2) over the overlap of lag k: for k > k0 that is <= sqrt(T_i H_j), for
+            // k < -k0 <= sqrt(H_i T_j).  Unless the maximum found beats both bounds the window is redone over all lags.
+            const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
+            const double* pj = g.part + ((int64_t)wl * g.C + j) * 2;
+            const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
+            if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.wfail[wl] = 1;
+        }
         // consistency guard: the exact maximum must sit where the screen saw it
         const float ee = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
         if (!(ee <= 0.25f * XF_TAU32)) {
@@ -865,8 +911,20 @@ static xv_kernel pick_verify(int N, int C, size_t smem_optin, int* ib) {
     return nullptr;
 }
 
+// Stage-A plan of the two-stage lag search: the longest transform that is at most 0.7 (else 0.8) of the full one and
+// still covers |lag| <= N/5; nullptr if there is none.
+static const XfPlan* pick_stage_a(int N, const XfPlan* full) {
+    const XfPlan* best = nullptr;
+    for (double frac : {0.7, 0.8}) {
+        for (const XfPlan& p : plans(true))
+            if (p.L < full->L && p.L <= frac * full->L && p.L >= N + N / 5) best = &p;
+        if (best) return best;
+    }
+    return nullptr;
+}
+
 int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
-                   int max_lag, int32_t* lag, double* cmax, bool fp32) {
+                   int max_lag, int32_t* lag, double* cmax, bool fp32, bool two_stage) {
     if (W <= 0) return NBLS_OK;
     const XfPlan* pl = pick_plan(N, max_lag, fp32);
     if (!pl) {
@@ -878,10 +936,17 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     const int P = C * (C - 1) / 2;
     NBLS_REQUIRE((int64_t)W * P < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld",
                  (long long)W * P);
-    const int SP = pl->L / 2 + 1;
-    const void* tw = nullptr;
+    const int lag_full = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
+    // two-stage search: only for the full-lag request of the FP32 screen, and not while recent bands kept failing
+    const XfPlan* pa = nullptr;
+    if (fp32 && two_stage && lag_full == N - 1 && !getenv("NBLS_NO_TWO_STAGE")) {
+        if (ctx->ts_skip > 0) --ctx->ts_skip;
+        else pa = pick_stage_a(N, pl);
+    }
+    const void *tw = nullptr, *twa = nullptr;
     if (fp32) NBLS_CHECK(twiddles<float2>(ctx, pl->L, &tw));
     else NBLS_CHECK(twiddles<double2>(ctx, pl->L, &tw));
+    if (pa) NBLS_CHECK(twiddles<float2>(ctx, pa->L, &twa));
     int ib = 0;
     xv_kernel verify = nullptr;
     size_t vsmem = 0;
@@ -892,45 +957,53 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         NBLS_CUDA(cudaFuncSetAttribute(verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
     }
     // windows per batch: spectra workspace bounded (they are re-read from L2 window by window)
+    const int SP = pl->L / 2 + 1;
     const size_t per_win = (size_t)C * SP * (fp32 ? sizeof(float2) : sizeof(double2));
     const size_t budget = (size_t)4 << 30;
     const int ncp = (C + 1) / 2, npp = (P + 1) / 2;
     int wb = (int)std::min<int64_t>(W, std::max<int64_t>(1, (int64_t)(budget / per_win)));
     wb = (int)std::min<int64_t>(wb, ((1LL << 31) - 1) / std::max(npp, ncp));
     NBLS_CHECK(ensure(ctx, ctx->spec, (size_t)wb * per_win));
-    NBLS_CHECK(ensure(ctx, ctx->energy, (size_t)wb * C * sizeof(double)));
+    NBLS_CHECK(ensure(ctx, ctx->energy, (size_t)wb * C * 3 * sizeof(double)));
     NBLS_CHECK(ensure(ctx, ctx->flags, ((size_t)wb * P + 4) * sizeof(int)));
     if (!ctx->xstat.p) {
-        NBLS_CHECK(ensure(ctx, ctx->xstat, 4 * sizeof(unsigned long long)));
-        NBLS_CUDA(cudaMemsetAsync(ctx->xstat.p, 0, 4 * sizeof(unsigned long long), ctx->stream));
+        NBLS_CHECK(ensure(ctx, ctx->xstat, 8 * sizeof(unsigned long long)));
+        NBLS_CUDA(cudaMemsetAsync(ctx->xstat.p, 0, 8 * sizeof(unsigned long long), ctx->stream));
     }
     if (fp32) {
         NBLS_CHECK(ensure(ctx, ctx->cand, (size_t)wb * P * XF_KC * sizeof(int32_t)));
         NBLS_CHECK(ensure(ctx, ctx->sval, (size_t)wb * P * sizeof(float)));
     }
-    NBLS_CUDA(cudaFuncSetAttribute(pl->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
-    NBLS_CUDA(cudaFuncSetAttribute(pl->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl->smem));
+    if (pa) NBLS_CHECK(ensure(ctx, ctx->wfail, (size_t)wb * 2 * sizeof(int)));
+    for (const XfPlan* q : {pl, pa}) {
+        if (!q) continue;
+        NBLS_CUDA(cudaFuncSetAttribute(q->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q->smem));
+        NBLS_CUDA(cudaFuncSetAttribute(q->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q->smem));
+    }
 
     XfArgs a;
     memset(&a, 0, sizeof(a));
     a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first;
-    a.lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
-    a.SP = SP; a.tw = tw;
     a.spec = ctx->spec.p;
     a.energy = (double*)ctx->energy.p;
+    a.part = a.energy + (size_t)wb * C;
     a.lag = lag; a.cmax = cmax;
     a.flag_count = (int*)ctx->flags.p;
     a.flag_list = a.flag_count + 4;
     a.cand = (int32_t*)ctx->cand.p;
     a.sval = (float*)ctx->sval.p;
     a.stat = (unsigned long long*)ctx->xstat.p;
-    for (int w0 = 0; w0 < W; w0 += wb) {
-        a.w0 = w0;
-        a.wn = std::min(wb, W - w0);
+    a.lag_dead = -lag_full;
+    a.wfail = (int*)ctx->wfail.p;
+    int* dwlist = a.wfail ? a.wfail + wb : nullptr;
+    std::vector<int> hfail, hlist;
+
+    // one pass of spectra -> pair -> (verify) -> time-domain list over the windows described by `a`
+    auto pass = [&](const XfPlan* q) -> int {
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
-        pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);
+        q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
         NBLS_CUDA(cudaGetLastError());
-        pl->pair<<<(unsigned)(a.wn * npp), pl->threads, pl->smem, ctx->stream>>>(a);
+        q->pair<<<(unsigned)(a.wn * npp), q->threads, q->smem, ctx->stream>>>(a);
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 2;
         if (fp32) {
@@ -940,8 +1013,44 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
             ctx->launches += 1;
         }
         // undecided arg-maxima are settled by the time-domain kernel (normally an empty list)
-        NBLS_CHECK(xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
-                                     ctx->sm_count * 2));
+        return xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
+                                 ctx->sm_count * 2);
+    };
+    int64_t n_redo = 0;
+    for (int w0 = 0; w0 < W; w0 += wb) {
+        const int wn = std::min(wb, W - w0);
+        a.w0 = w0;
+        if (pa) {
+            // stage A: |lag| <= k0 with the shorter transform, plus the proof that nothing beyond k0 can win
+            a.wn = wn; a.wlist = nullptr;
+            a.k0 = std::min(pa->L - N, N - 1); a.lag_max = a.k0;
+            a.SP = pa->L / 2 + 1; a.tw = twa;
+            NBLS_CUDA(cudaMemsetAsync(a.wfail, 0, (size_t)wn * sizeof(int), ctx->stream));
+            NBLS_CHECK(pass(pa));
+            hfail.resize(wn);
+            NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+            hlist.clear();
+            for (int i = 0; i < wn; ++i)
+                if (hfail[i]) hlist.push_back(w0 + i);
+            n_redo += (int64_t)hlist.size();
+            if (hlist.empty()) continue;
+            // stage B: the windows without a proof, over all lags
+            NBLS_CUDA(cudaMemcpyAsync(dwlist, hlist.data(), hlist.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+            NBLS_CUDA(cudaStreamSynchronize(ctx->stream));     // hlist is pageable and reused
+            a.wn = (int)hlist.size(); a.wlist = dwlist;
+        } else {
+            a.wn = wn; a.wlist = nullptr;
+        }
+        a.k0 = -1; a.lag_max = lag_full;
+        a.SP = SP; a.tw = tw;
+        NBLS_CHECK(pass(pl));
+    }
+    if (pa) {
+        ctx->ts_windows += W;
+        ctx->ts_redone += n_redo;
+        // a band where most windows had to be redone: leave the next three bands to the single-stage search
+        if (n_redo * 2 > (int64_t)W) ctx->ts_skip = 3;
     }
     return NBLS_OK;
 }

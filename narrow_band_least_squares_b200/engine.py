@@ -235,7 +235,10 @@ class Engine:
         time-domain kernel settled, largest |FP32 screen maximum - exact maximum| seen."""
         nv, nt, err = C.c_int64(), C.c_int64(), C.c_double()
         check(self.lib.nbls_xcorr_stats(self.ctx, C.byref(nv), C.byref(nt), C.byref(err), int(bool(reset))))
-        return dict(verified=nv.value, time_domain=nt.value, max_screen_err=err.value)
+        nw, nr = C.c_int64(), C.c_int64()
+        check(self.lib.nbls_xcorr_two_stage_stats(self.ctx, C.byref(nw), C.byref(nr), int(bool(reset))))
+        return dict(verified=nv.value, time_domain=nt.value, max_screen_err=err.value, two_stage_windows=nw.value,
+                    two_stage_redone=nr.value)
 
     # ---- stage level ------------------------------------------------------------------------
     def filter_bands(self, data, fs, sos_list, zerophase=True, taper=0.01, chunk_len=0, exact_scan=False,

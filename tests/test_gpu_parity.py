@@ -317,17 +317,22 @@ def test_c3_sized_methods_agree_end_to_end(eng):
     from narrow_band_least_squares_b200.synth import config_record
     rec = config_record("c3", hours=0.25)
     out = {}
-    for name, method in (("fft32", _capi.XCORR_FFT32), ("fft64", _capi.XCORR_FFT), ("direct", _capi.XCORR_DIRECT)):
+    for name, method in (("fft32", _capi.XCORR_FFT32), ("auto", _capi.XCORR_AUTO), ("fft64", _capi.XCORR_FFT),
+                         ("direct", _capi.XCORR_DIRECT)):
         plan = config_plan("c3", rec.npts, rec.rij, method=method)
-        if name == "fft32":
+        if name in ("fft32", "auto"):
             eng.xcorr_stats(reset=True)
         res = eng.run(plan, rec.data, Results(plan, pinned=False))
         if name == "fft32":
             st = eng.xcorr_stats(reset=True)
+        if name == "auto":
+            st2 = eng.xcorr_stats(reset=True)
         out[name] = {k: np.array(getattr(res, k)[:plan.nwin]) for k in ("lag", "cmax", "vel", "baz", "mdccm", "sigma_tau")}
         nwin, npairs = plan.nwin, plan.npairs
     assert npairs == 300 and nwin > 600
-    for other in ("fft64", "direct"):
+    # two-stage search of AUTO: every window went through stage A, the noise-only minute (and little else) needed stage B
+    assert st2["two_stage_windows"] == nwin and 0 < st2["two_stage_redone"] < 0.5 * nwin, st2
+    for other in ("auto", "fft64", "direct"):
         assert np.array_equal(out["fft32"]["lag"], out[other]["lag"]), other
         assert np.allclose(out["fft32"]["cmax"], out[other]["cmax"], rtol=0, atol=1e-12, equal_nan=True), other
         for k in ("vel", "baz", "mdccm", "sigma_tau"):
