@@ -912,12 +912,12 @@ static xv_kernel pick_verify(int N, int C, size_t smem_optin, int* ib) {
 }
 
 // Stage-A plan of the two-stage lag search: the longest transform that is at most 0.7 (else 0.8) of the full one and
-// still covers |lag| <= N/5; nullptr if there is none.
+// still covers |lag| <= N/4; nullptr if there is none.
 static const XfPlan* pick_stage_a(int N, const XfPlan* full) {
     const XfPlan* best = nullptr;
     for (double frac : {0.7, 0.8}) {
         for (const XfPlan& p : plans(true))
-            if (p.L < full->L && p.L <= frac * full->L && p.L >= N + N / 5) best = &p;
+            if (p.L < full->L && p.L <= frac * full->L && p.L >= N + N / 4) best = &p;
         if (best) return best;
     }
     return nullptr;

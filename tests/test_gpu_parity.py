@@ -330,8 +330,9 @@ def test_c3_sized_methods_agree_end_to_end(eng):
         out[name] = {k: np.array(getattr(res, k)[:plan.nwin]) for k in ("lag", "cmax", "vel", "baz", "mdccm", "sigma_tau")}
         nwin, npairs = plan.nwin, plan.npairs
     assert npairs == 300 and nwin > 600
-    # two-stage search of AUTO: every window went through stage A, the noise-only minute (and little else) needed stage B
-    assert st2["two_stage_windows"] == nwin and 0 < st2["two_stage_redone"] < 0.5 * nwin, st2
+    # two-stage search of AUTO: (nearly) every window went through stage A - a band where most windows fail hands the next
+    # three bands to the single-stage search - and the noise-only minute (and little else) needed stage B
+    assert 0.5 * nwin < st2["two_stage_windows"] <= nwin and 0 < st2["two_stage_redone"] < 0.5 * nwin, st2
     for other in ("auto", "fft64", "direct"):
         assert np.array_equal(out["fft32"]["lag"], out[other]["lag"]), other
         assert np.allclose(out["fft32"]["cmax"], out[other]["cmax"], rtol=0, atol=1e-12, equal_nan=True), other
