@@ -381,6 +381,9 @@ def main():
                                         "bound).  FFT butterflies are mostly unfused adds, so 0.5 is the ceiling of this "
                                         "fraction; ncu (profiles/) gives the issue-slot utilisation of the pair kernel",
                          "algorithmic_flop_per_step": work, "fp64_verify_flop_per_step": flop64 if use32 else None,
+                         "note": ("algorithmic = the single-stage search over all 2N-1 lags; with --method auto the "
+                                  "two-stage search executes less (xcorr_stats.two_stage_*), so 'achieved' is "
+                                  "algorithmic work per second, not executed flop/s") if args.method == "auto" else None,
                          "fp64_peak": r["fp64_peak"], "fp32_peak": r["fp32_peak"]},
             "roofline_filter": {"kernel": "biquad_chunk_kernel x6 + carry x2", "bound": "hbm", "achieved": fgb,
                                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (fgb / peaks["hbm_gbs"]) if fgb else None,
