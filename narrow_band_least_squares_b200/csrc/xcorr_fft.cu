@@ -593,9 +593,7 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
 // without bounds checks.  Slice sums are combined in a fixed order (deterministic); further candidates (near-ties,
 // ~5 % of the pairs) are evaluated warp by warp afterwards.  The largest exact value wins, the lowest lag on an
 // exact tie (np.argmax); cmax = value / sqrt(Ei Ej).
-constexpr int XV_WARPS = 32;
-constexpr int XV_SL = 8;
-constexpr int XV_JG = XV_WARPS / XV_SL;
+constexpr int XV_SL = 8;      // time slices of a window; a CTA has 32 warps (one per SM) or 16 (two per SM)
 static_assert(XF_KC <= 4, "work-list entries pack the candidate slot in two bits");
 
 static size_t verify_smem(int IB, int N, int C) {
@@ -636,8 +634,9 @@ __device__ __forceinline__ void verify_slice(const double* xj, const double* xs,
     }
 }
 
-template <int IB>
-__global__ void __launch_bounds__(XV_WARPS * 32, 1) xf_verify_kernel(XfArgs g) {
+template <int IB, int NW>
+__global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
+    constexpr int XV_WARPS = NW, XV_JG = NW / XV_SL;
     extern __shared__ __align__(16) unsigned char xf_smem_raw[];
     const int N = g.N, NJ = g.C - 1;
     double* xs = reinterpret_cast<double*>(xf_smem_raw);     // [IB][N]
@@ -904,10 +903,16 @@ static int twiddles(nbls_ctx* ctx, int L, const void** out) {
 }
 
 typedef void (*xv_kernel)(XfArgs);
-static xv_kernel pick_verify(int N, int C, size_t smem_optin, int* ib) {
-    if (verify_smem(4, N, C) <= smem_optin - 1024) { *ib = 4; return xf_verify_kernel<4>; }
-    if (verify_smem(2, N, C) <= smem_optin - 1024) { *ib = 2; return xf_verify_kernel<2>; }
-    if (verify_smem(1, N, C) <= smem_optin - 1024) { *ib = 1; return xf_verify_kernel<1>; }
+static xv_kernel pick_verify(int N, int C, size_t smem_optin, int* ib, int* nw) {
+    const size_t sm_total = 228 * 1024, half = sm_total / 2 - 2048;     // two CTAs per SM must both fit
+    // two 16-warp CTAs per SM (one stages while the other computes) beat one 32-warp CTA even at half the channel block:
+    // c3 2 h 8.8 -> 7.5 ms
+    *nw = 32;
+    if (verify_smem(4, N, C) <= half) { *ib = 4; *nw = 16; return xf_verify_kernel<4, 16>; }
+    if (verify_smem(2, N, C) <= half) { *ib = 2; *nw = 16; return xf_verify_kernel<2, 16>; }
+    if (verify_smem(4, N, C) <= smem_optin - 1024) { *ib = 4; return xf_verify_kernel<4, 32>; }
+    if (verify_smem(2, N, C) <= smem_optin - 1024) { *ib = 2; return xf_verify_kernel<2, 32>; }
+    if (verify_smem(1, N, C) <= smem_optin - 1024) { *ib = 1; return xf_verify_kernel<1, 32>; }
     return nullptr;
 }
 
@@ -947,11 +952,11 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     if (fp32) NBLS_CHECK(twiddles<float2>(ctx, pl->L, &tw));
     else NBLS_CHECK(twiddles<double2>(ctx, pl->L, &tw));
     if (pa) NBLS_CHECK(twiddles<float2>(ctx, pa->L, &twa));
-    int ib = 0;
+    int ib = 0, vnw = 32;
     xv_kernel verify = nullptr;
     size_t vsmem = 0;
     if (fp32) {
-        verify = pick_verify(N, C, ctx->smem_optin, &ib);
+        verify = pick_verify(N, C, ctx->smem_optin, &ib, &vnw);
         NBLS_REQUIRE(verify, "nbls_xcorr(fft32): a window of %d samples does not fit in shared memory", N);
         vsmem = verify_smem(ib, N, C);
         NBLS_CUDA(cudaFuncSetAttribute(verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
@@ -1008,7 +1013,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         ctx->launches += 2;
         if (fp32) {
             const int nib = (C - 1 + ib - 1) / ib;
-            verify<<<(unsigned)(a.wn * nib), XV_WARPS * 32, vsmem, ctx->stream>>>(a);
+            verify<<<(unsigned)(a.wn * nib), vnw * 32, vsmem, ctx->stream>>>(a);
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 1;
         }
