@@ -65,6 +65,7 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
     NBLS_CHECK(validate_windows(w, C, ldy, &E));
     const int P = C * (C - 1) / 2;
     int64_t row = 0;
+    ctx->ts_skip = 0;      // the two-stage search adapts within a call only: identical calls give identical bits
     for (int b = 0; b < w->nbands; ++b) {
         const int N = w->win_len[b], W = w->win_count[b];
         int method = w->method;
