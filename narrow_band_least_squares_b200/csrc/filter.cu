@@ -18,6 +18,7 @@
 // eight lanes per 128-B line) into a padded shared-memory tile, lane r computes row r, and the
 // results leave through the same tile as full 128-B lines.
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -28,7 +29,7 @@
 
 namespace nbls {
 
-constexpr int FT_TILE = 16;    // samples per chunk per step (one 128-B line; 32 = 256 B was measured: no gain)
+constexpr int FT_TILE = 32;    // samples per chunk per step (one 128-B line; 32 = 256 B was measured: no gain)
 constexpr int FT_ROW = FT_TILE + 2;   // padded row stride in doubles: (8 TILE + 16) B keeps 16-B alignment and
                                // makes lane r's LDS.128 hit banks 4r..4r+3 (conflict-free)
 constexpr int FT_STAGES = 3;   // cp.async ring depth
@@ -344,7 +345,8 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     // chunking
     int64_t L = d->chunk_len;
     if (L <= 0) {
-        L = round_up((int64_t)((double)T * B * C / 131072.0), FT_TILE);
+        const double lanes = getenv("NBLS_FILTER_LANES") ? atof(getenv("NBLS_FILTER_LANES")) : 131072.0;
+        L = round_up((int64_t)((double)T * B * C / lanes), FT_TILE);
         L = std::max<int64_t>(256, std::min<int64_t>(65536, L));
     }
     NBLS_REQUIRE(L % FT_TILE == 0 && L >= FT_TILE, "nbls_filter: chunk_len must be a positive multiple of %d", FT_TILE);
