@@ -78,9 +78,18 @@ struct XfArgs {
     double* part;         // stage A: [wn][C][2] = sum of x^2 over n < N-k0-1 (head) and over n > k0 (tail)
     int* wfail;           // stage A: [wn] set to 1 when some pair of the window fails the proof
     const int* wlist;     // stage B: band-level window index of batch slot wl; nullptr = w0 + wl
+    // probe: before stage A runs on a batch, `npp_run` pair-pairs of every window go through the stage-A pair kernel
+    // alone.  A probe pair whose FP32 maximum is clearly below its Cauchy-Schwarz bound cannot pass the proof, so the
+    // window is sent straight to stage B (a routing decision only - stage B is always exact).  Stage A then runs in
+    // window-list mode on the remaining windows and re-uses the probe's spectra (spec_by_win).
+    int probe;            // pair kernel: only decide wfail[wl] from the screen maximum, write nothing else
+    int npp_run;          // pair-pairs per window in this launch (probe); 0 = all
+    int spec_by_win;      // spec / energy / part rows are indexed by (window - w0) instead of the list slot wl
 };
 
 __device__ __forceinline__ int win_index(const XfArgs& g, int wl) { return g.wlist ? g.wlist[wl] : g.w0 + wl; }
+// row of spec / energy / part that holds batch slot wl
+__device__ __forceinline__ int spec_slot(const XfArgs& g, int wl) { return g.spec_by_win ? win_index(g, wl) - g.w0 : wl; }
 
 template <int R1_, int R2_, int R3_>
 struct Shape {
@@ -301,13 +310,17 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     constexpr int R1 = S::R1, L = S::L, M1 = S::M1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int npp = (g.P + 1) >> 1;
-    const int wl = blockIdx.x / npp, q = blockIdx.x - wl * npp;
+    const int nrun = g.npp_run > 0 ? g.npp_run : npp;
+    const int wl = blockIdx.x / nrun;
+    int q = blockIdx.x - wl * nrun;
+    if (g.npp_run > 0) q = (int)(((int64_t)q * npp) / nrun);     // probe: pair-pairs spread over the pair list
+    const int ws = spec_slot(g, wl);
     const int p0 = 2 * q, p1 = 2 * q + 1;
     const bool has1 = p1 < g.P;
     int i0, j0, i1, j1;
     pair_channels(p0, g.C, i0, j0);
     pair_channels(has1 ? p1 : p0, g.C, i1, j1);
-    const V* sbase = static_cast<const V*>(g.spec) + (int64_t)wl * g.C * g.SP;
+    const V* sbase = static_cast<const V*>(g.spec) + (int64_t)ws * g.C * g.SP;
     const V *Xi0 = sbase + (int64_t)i0 * g.SP, *Xj0 = sbase + (int64_t)j0 * g.SP;
     const V *Xi1 = sbase + (int64_t)i1 * g.SP, *Xj1 = sbase + (int64_t)j1 * g.SP;
     const bool same_i = i0 == i1;
@@ -484,8 +497,19 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         if (tid < 2 && (tid == 0 || has1)) {
             const int p = tid == 0 ? p0 : p1;
             const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
-            const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
+            const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + cj];
             const double den = sqrt(Ei * Ej);
+            if (g.probe) {
+                // the screen maximum over |lag| <= k0 against the bound on every lag beyond k0 (see xf_verify_kernel)
+                if (den > 0.0 && isfinite(den)) {
+                    const double* pi = g.part + ((int64_t)ws * g.C + ci) * 2;
+                    const double* pj = g.part + ((int64_t)ws * g.C + cj) * 2;
+                    const double bound = sqrt(fmax(pi[1] * pj[0], pi[0] * pj[1])) / den;
+                    const double m32 = (double)((tid == 0 ? mr : mi) / (float)L);
+                    if (m32 + 1e-4 < bound) g.wfail[wl] = 1;
+                }
+                return;
+            }
             const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
             const int64_t loc = (int64_t)wl * g.P + p;
             const int cnt = scnt[tid];
@@ -563,7 +587,7 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         for (int i = 1; i < T / 32; ++i) top_merge(b, rb1[tid][i], rb2[tid][i], rl1[tid][i]);
         const int p = tid == 0 ? p0 : p1;
         const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
-        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
+        const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + cj];
         const double den = sqrt(Ei * Ej);
         const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
         if (!(den > 0.0)) {
@@ -781,7 +805,8 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
             if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
             ++ncand;
         }
-        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
+        const int ws = spec_slot(g, wl);
+        const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + j];
         const double c = best / sqrt(Ei * Ej);
         const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
         g.lag[item] = bl;
@@ -789,8 +814,8 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
         if (g.k0 >= 0) {
             // |c[k]| <= sqrt(sum x_i^2 * sum x_j^2) over the overlap of lag k: for k > k0 that is <= sqrt(T_i H_j), for
             // k < -k0 <= sqrt(H_i T_j).  Unless the maximum found beats both bounds the window is redone over all lags.
-            const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
-            const double* pj = g.part + ((int64_t)wl * g.C + j) * 2;
+            const double* pi = g.part + ((int64_t)ws * g.C + ci) * 2;
+            const double* pj = g.part + ((int64_t)ws * g.C + j) * 2;
             const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
             if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.wfail[wl] = 1;
         }
@@ -1001,16 +1026,21 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     a.lag_dead = -lag_full;
     a.wfail = (int*)ctx->wfail.p;
     int* dwlist = a.wfail ? a.wfail + wb : nullptr;
-    std::vector<int> hfail, hlist;
+    std::vector<int> hfail, hlist, hlistA;
+    const bool use_probe = pa && !getenv("NBLS_NO_PROBE");
+    const int probe_pp = getenv("NBLS_PROBE_PP") ? std::max(1, atoi(getenv("NBLS_PROBE_PP"))) : 2;
 
     // one pass of spectra -> pair -> (verify) -> time-domain list over the windows described by `a`
-    auto pass = [&](const XfPlan* q) -> int {
+    auto pass = [&](const XfPlan* q, bool with_spectra) -> int {
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
-        q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
-        NBLS_CUDA(cudaGetLastError());
+        if (with_spectra) {
+            q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
+            NBLS_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+        }
         q->pair<<<(unsigned)(a.wn * npp), q->threads, q->smem, ctx->stream>>>(a);
         NBLS_CUDA(cudaGetLastError());
-        ctx->launches += 2;
+        ctx->launches += 1;
         if (fp32) {
             const int nib = (C - 1 + ib - 1) / ib;
             verify<<<(unsigned)(a.wn * nib), vnw * 32, vsmem, ctx->stream>>>(a);
@@ -1031,13 +1061,44 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
             a.k0 = std::min(pa->L - N, N - 1); a.lag_max = a.k0;
             a.SP = pa->L / 2 + 1; a.tw = twa;
             NBLS_CUDA(cudaMemsetAsync(a.wfail, 0, (size_t)wn * sizeof(int), ctx->stream));
-            NBLS_CHECK(pass(pa));
             hfail.resize(wn);
-            NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-            NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
             hlist.clear();
-            for (int i = 0; i < wn; ++i)
-                if (hfail[i]) hlist.push_back(w0 + i);
+            if (use_probe) {
+                // probe: spectra of the whole batch, then two pair-pairs per window decide which windows cannot pass
+                pa->spectra<<<(unsigned)(wn * ncp), pa->threads, pa->smem, ctx->stream>>>(a);
+                NBLS_CUDA(cudaGetLastError());
+                a.probe = 1; a.npp_run = std::min(probe_pp, npp);
+                pa->pair<<<(unsigned)(wn * a.npp_run), pa->threads, pa->smem, ctx->stream>>>(a);
+                NBLS_CUDA(cudaGetLastError());
+                a.probe = 0; a.npp_run = 0;
+                ctx->launches += 2;
+                NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost,
+                                          ctx->stream));
+                NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+                hlistA.clear();
+                for (int i = 0; i < wn; ++i) (hfail[i] ? hlist : hlistA).push_back(w0 + i);
+                if (!hlistA.empty()) {
+                    NBLS_CUDA(cudaMemsetAsync(a.wfail, 0, (size_t)wn * sizeof(int), ctx->stream));
+                    NBLS_CUDA(cudaMemcpyAsync(dwlist, hlistA.data(), hlistA.size() * sizeof(int), cudaMemcpyHostToDevice,
+                                              ctx->stream));
+                    a.wn = (int)hlistA.size(); a.wlist = dwlist; a.spec_by_win = 1;
+                    NBLS_CHECK(pass(pa, false));
+                    a.spec_by_win = 0;
+                    NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, hlistA.size() * sizeof(int), cudaMemcpyDeviceToHost,
+                                              ctx->stream));
+                    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));   // also: hlistA is pageable and reused
+                    for (size_t i = 0; i < hlistA.size(); ++i)
+                        if (hfail[i]) hlist.push_back(hlistA[i]);
+                    std::sort(hlist.begin(), hlist.end());
+                }
+            } else {
+                NBLS_CHECK(pass(pa, true));
+                NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost,
+                                          ctx->stream));
+                NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+                for (int i = 0; i < wn; ++i)
+                    if (hfail[i]) hlist.push_back(w0 + i);
+            }
             n_redo += (int64_t)hlist.size();
             if (hlist.empty()) continue;
             // stage B: the windows without a proof, over all lags
@@ -1049,7 +1110,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         }
         a.k0 = -1; a.lag_max = lag_full;
         a.SP = SP; a.tw = tw;
-        NBLS_CHECK(pass(pl));
+        NBLS_CHECK(pass(pl, true));
     }
     if (pa) {
         ctx->ts_windows += W;
