@@ -60,7 +60,7 @@ struct nbls_ctx {
     nbls::DevBuf coef, state, carry, taper, filt, geom, lts_tab, xin, res, lagbuf, cmaxbuf, wbuf, scratch;
     nbls::DevBuf spec, energy, flags;       // FFT cross-correlation workspace
     nbls::DevBuf cand, sval, xstat;         // FP32 screen: candidate lags, screen maxima; xcorr statistics
-    nbls::DevBuf wfail;                     // two-stage lag search: failed-window flags and list
+    nbls::DevBuf wfail;                     // two-stage lag search: failing pair-window items and the window list of stage B
     int ts_skip = 0;                        // bands left to the single-stage search after a band that mostly failed
     int64_t ts_windows = 0, ts_redone = 0;  // two-stage statistics: windows searched / redone over all lags
     std::map<int, void*> fft_tw;            // twiddle tables by transform length (device)

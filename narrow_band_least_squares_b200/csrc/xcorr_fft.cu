@@ -66,30 +66,27 @@ struct XfArgs {
     double* cmax;         // [W][P] or nullptr
     int* flag_list;       // [>= wn*P] items w*P+p (band level) to re-evaluate in the time domain
     int* flag_count;
-    int32_t* cand;        // FP32 screen: [wn*P][XF_KC] candidate lags of batch item wl*P+p, INT_MIN = unused
-    float* sval;          // FP32 screen: [wn*P] the FP32 maximum (normalised)
+    // spec, energy, part, cand and sval rows are indexed by wl = (band-level window index) - w0, whatever list the
+    // launch walks, so a later launch over a subset of the batch finds the rows of an earlier one
+    int32_t* cand;        // FP32 screen: [wb*P][XF_KC] candidate lags of batch item wl*P+p, INT_MIN = unused
+    float* sval;          // FP32 screen: [wb*P] the FP32 maximum (normalised)
     unsigned long long* stat;   // [0] candidates verified, [1] items sent to the time-domain kernel,
                                 // [2] max |FP32 max - exact max| as float bits
     // two-stage lag search (FP32 screen only).  Stage A searches |lag| <= k0 with a shorter transform and proves per
     // pair-window, by Cauchy-Schwarz over partial energies, that no lag beyond k0 can reach the maximum found; the
-    // windows where the proof fails for some pair are listed (wfail) and redone over all lags (stage B, wlist).
+    // pair-windows where the proof fails are listed (pf_list) and redone over all lags (stage B: spectra of their windows
+    // in window-list mode, pair kernel and xf_verify_items_kernel in item mode).
     int k0;               // stage A: lag bound of the search (>= 0); otherwise -1
     int lag_dead;         // lag written for a zero-energy pair: -(N-1) or -max_lag of the request
     double* part;         // stage A: [wn][C][2] = sum of x^2 over n < N-k0-1 (head) and over n > k0 (tail)
-    int* wfail;           // stage A: [wn] set to 1 when some pair of the window fails the proof
-    const int* wlist;     // stage B: band-level window index of batch slot wl; nullptr = w0 + wl
-    // probe: before stage A runs on a batch, `npp_run` pair-pairs of every window go through the stage-A pair kernel
-    // alone.  A probe pair whose FP32 maximum is clearly below its Cauchy-Schwarz bound cannot pass the proof, so the
-    // window is sent straight to stage B (a routing decision only - stage B is always exact).  Stage A then runs in
-    // window-list mode on the remaining windows and re-uses the probe's spectra (spec_by_win).
-    int probe;            // pair kernel: only decide wfail[wl] from the screen maximum, write nothing else
-    int npp_run;          // pair-pairs per window in this launch (probe); 0 = all
-    int spec_by_win;      // spec / energy / part rows are indexed by (window - w0) instead of the list slot wl
+    int* pf_list;         // stage A out: batch items wl*P+p whose proof failed (unordered; the host sorts them)
+    int* pf_count;
+    const int* wlist;     // window-list mode: band-level window index of launch slot s; nullptr = w0 + s
+    const int* items;     // item mode (pair kernel, xf_verify_items_kernel): sorted batch items wl*P+p, two per pair CTA
+    int n_items;
 };
 
-__device__ __forceinline__ int win_index(const XfArgs& g, int wl) { return g.wlist ? g.wlist[wl] : g.w0 + wl; }
-// row of spec / energy / part that holds batch slot wl
-__device__ __forceinline__ int spec_slot(const XfArgs& g, int wl) { return g.spec_by_win ? win_index(g, wl) - g.w0 : wl; }
+__device__ __forceinline__ int win_index(const XfArgs& g, int s) { return g.wlist ? g.wlist[s] : g.w0 + s; }
 
 template <int R1_, int R2_, int R3_>
 struct Shape {
@@ -155,10 +152,11 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     __shared__ double rs_sh[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ncp = (g.C + 1) >> 1;
-    const int wl = blockIdx.x / ncp, cp = blockIdx.x - wl * ncp;
+    const int wslot = blockIdx.x / ncp, cp = blockIdx.x - wslot * ncp;
+    const int wband = win_index(g, wslot), wl = wband - g.w0;
     const int ca = 2 * cp, cb = 2 * cp + 1;
     const bool has_b = cb < g.C;
-    const int64_t t0 = g.first + (int64_t)win_index(g, wl) * g.hop;
+    const int64_t t0 = g.first + (int64_t)wband * g.hop;
     const double* xa = g.y + (int64_t)ca * g.ldy + t0;
     const double* xb = g.y + (int64_t)(has_b ? cb : ca) * g.ldy + t0;
 
@@ -310,20 +308,30 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     constexpr int R1 = S::R1, L = S::L, M1 = S::M1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int npp = (g.P + 1) >> 1;
-    const int nrun = g.npp_run > 0 ? g.npp_run : npp;
-    const int wl = blockIdx.x / nrun;
-    int q = blockIdx.x - wl * nrun;
-    if (g.npp_run > 0) q = (int)(((int64_t)q * npp) / nrun);     // probe: pair-pairs spread over the pair list
-    const int ws = spec_slot(g, wl);
-    const int p0 = 2 * q, p1 = 2 * q + 1;
-    const bool has1 = p1 < g.P;
+    // the two riders of this CTA: (data row wl0, pair p0) on the real part, (wl1, p1) on the imaginary part
+    int wl0, wl1, p0, p1;
+    bool has1;
+    if (g.items) {
+        const int e0 = 2 * (int)blockIdx.x, e1 = e0 + 1;
+        has1 = e1 < g.n_items;
+        const int it0 = g.items[e0], it1 = g.items[has1 ? e1 : e0];
+        wl0 = it0 / g.P; p0 = it0 - wl0 * g.P;
+        wl1 = it1 / g.P; p1 = it1 - wl1 * g.P;
+    } else {
+        const int wslot = blockIdx.x / npp, q = blockIdx.x - wslot * npp;
+        wl0 = wl1 = win_index(g, wslot) - g.w0;
+        p0 = 2 * q; p1 = 2 * q + 1;
+        has1 = p1 < g.P;
+        if (!has1) p1 = p0;
+    }
     int i0, j0, i1, j1;
     pair_channels(p0, g.C, i0, j0);
-    pair_channels(has1 ? p1 : p0, g.C, i1, j1);
-    const V* sbase = static_cast<const V*>(g.spec) + (int64_t)ws * g.C * g.SP;
-    const V *Xi0 = sbase + (int64_t)i0 * g.SP, *Xj0 = sbase + (int64_t)j0 * g.SP;
-    const V *Xi1 = sbase + (int64_t)i1 * g.SP, *Xj1 = sbase + (int64_t)j1 * g.SP;
-    const bool same_i = i0 == i1;
+    pair_channels(p1, g.C, i1, j1);
+    const V* sbase0 = static_cast<const V*>(g.spec) + (int64_t)wl0 * g.C * g.SP;
+    const V* sbase1 = static_cast<const V*>(g.spec) + (int64_t)wl1 * g.C * g.SP;
+    const V *Xi0 = sbase0 + (int64_t)i0 * g.SP, *Xj0 = sbase0 + (int64_t)j0 * g.SP;
+    const V *Xi1 = sbase1 + (int64_t)i1 * g.SP, *Xj1 = sbase1 + (int64_t)j1 * g.SP;
+    const bool same_i = i0 == i1 && wl0 == wl1;
 
     // cross-spectra of entry gidx: a = X_i0 conj(X_j0), b = X_i1 conj(X_j1)
     auto cross = [&](int gidx, V& a, V& b) {
@@ -495,22 +503,11 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         }
         __syncthreads();
         if (tid < 2 && (tid == 0 || has1)) {
-            const int p = tid == 0 ? p0 : p1;
+            const int p = tid == 0 ? p0 : p1, wl = tid == 0 ? wl0 : wl1;
             const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
-            const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + cj];
+            const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
             const double den = sqrt(Ei * Ej);
-            if (g.probe) {
-                // the screen maximum over |lag| <= k0 against the bound on every lag beyond k0 (see xf_verify_kernel)
-                if (den > 0.0 && isfinite(den)) {
-                    const double* pi = g.part + ((int64_t)ws * g.C + ci) * 2;
-                    const double* pj = g.part + ((int64_t)ws * g.C + cj) * 2;
-                    const double bound = sqrt(fmax(pi[1] * pj[0], pi[0] * pj[1])) / den;
-                    const double m32 = (double)((tid == 0 ? mr : mi) / (float)L);
-                    if (m32 + 1e-4 < bound) g.wfail[wl] = 1;
-                }
-                return;
-            }
-            const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
+            const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
             const int64_t loc = (int64_t)wl * g.P + p;
             const int cnt = scnt[tid];
             int32_t* cd = g.cand + loc * XF_KC;
@@ -585,11 +582,11 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     if (tid < 2 && (tid == 0 || has1)) {
         Top b = {rb1[tid][0], rb2[tid][0], rl1[tid][0]};
         for (int i = 1; i < T / 32; ++i) top_merge(b, rb1[tid][i], rb2[tid][i], rl1[tid][i]);
-        const int p = tid == 0 ? p0 : p1;
+        const int p = tid == 0 ? p0 : p1, wl = tid == 0 ? wl0 : wl1;
         const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
-        const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + cj];
+        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
         const double den = sqrt(Ei * Ej);
-        const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
+        const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
         if (!(den > 0.0)) {
             // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched
             g.lag[item] = g.lag_dead;
@@ -674,9 +671,10 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
     __shared__ unsigned int wcnt[XV_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nib = (g.C - 1 + IB - 1) / IB;
-    const int wl = blockIdx.x / nib, ib = blockIdx.x - wl * nib;
+    const int wslot = blockIdx.x / nib, ib = blockIdx.x - wslot * nib;
+    const int wband = win_index(g, wslot), wl = wband - g.w0;
     const int i_base = ib * IB;
-    const int64_t t0 = g.first + (int64_t)win_index(g, wl) * g.hop;
+    const int64_t t0 = g.first + (int64_t)wband * g.hop;
     if (tid == 0) ecount = 0;
     const int njj = g.C - 1 - i_base;                    // channels j = i_base+1 .. C-1
     for (int e = tid; e < njj * IB; e += XV_WARPS * 32) {
@@ -805,19 +803,18 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
             if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
             ++ncand;
         }
-        const int ws = spec_slot(g, wl);
-        const double Ei = g.energy[(int64_t)ws * g.C + ci], Ej = g.energy[(int64_t)ws * g.C + j];
+        const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
         const double c = best / sqrt(Ei * Ej);
-        const int64_t item = (int64_t)win_index(g, wl) * g.P + p;
+        const int64_t item = (int64_t)wband * g.P + p;
         g.lag[item] = bl;
         if (g.cmax) g.cmax[item] = c;
         if (g.k0 >= 0) {
             // |c[k]| <= sqrt(sum x_i^2 * sum x_j^2) over the overlap of lag k: for k > k0 that is <= sqrt(T_i H_j), for
             // k < -k0 <= sqrt(H_i T_j).  Unless the maximum found beats both bounds the window is redone over all lags.
-            const double* pi = g.part + ((int64_t)ws * g.C + ci) * 2;
-            const double* pj = g.part + ((int64_t)ws * g.C + j) * 2;
+            const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
+            const double* pj = g.part + ((int64_t)wl * g.C + j) * 2;
             const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
-            if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.wfail[wl] = 1;
+            if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.pf_list[atomicAdd(g.pf_count, 1)] = wl * g.P + p;
         }
         // consistency guard: the exact maximum must sit where the screen saw it
         const float ee = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
@@ -841,6 +838,77 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
         for (int i = 0; i < XV_WARPS; ++i) { err = fmaxf(err, werr[i]); n += wcnt[i]; }
         atomicAdd(g.stat, n);
         atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(err));
+    }
+}
+
+// Item mode of the verification (stage B of the two-stage search): one CTA of XV_SL warps per listed pair-window.  The sums
+// are formed exactly like xf_verify_kernel forms them (same time slices, same per-lane order, same trees), so a
+// pair-window gets the same bits whichever kernel evaluates its candidates.
+__global__ void __launch_bounds__(XV_SL * 32) xf_verify_items_kernel(XfArgs g) {
+    extern __shared__ __align__(16) unsigned char xv_smem_raw[];
+    double* xs = reinterpret_cast<double*>(xv_smem_raw);     // [N] window of channel i
+    __shared__ double sp[XV_SL], se[XF_KC - 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int N = g.N;
+    const int it = g.items[blockIdx.x];
+    const int wl = it / g.P, p = it - wl * g.P;
+    const int32_t* cd = g.cand + (int64_t)it * XF_KC;
+    if (cd[0] == INT_MIN) return;            // dead pair or handed to the time-domain kernel by the pair kernel
+    int ci, j;
+    pair_channels(p, g.C, ci, j);
+    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+    {
+        const double* src = g.y + (int64_t)ci * g.ldy + t0;
+#pragma unroll 8
+        for (int n = tid; n < N; n += XV_SL * 32) xs[n] = __ldg(src + n);
+    }
+    __syncthreads();
+    const double* xj = g.y + (int64_t)j * g.ldy + t0;
+    {
+        const int SLN = ((N + XV_SL - 1) / XV_SL + 31) / 32 * 32;
+        const int a = min(N, warp * SLN), b = min(N, a + SLN);
+        const int k[1] = {cd[0]}, off[1] = {cd[0]};
+        double acc[1] = {0.0};
+        verify_slice<1, true>(xj, xs, off, k, a, b, N, lane, acc);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], o);
+        if (lane == 0) sp[warp] = acc[0];
+    }
+    if (warp + 1 < XF_KC && cd[warp + 1] != INT_MIN) {
+        const int ks = cd[warp + 1];
+        const int nlo = max(0, -ks), nhi = min(N, N - ks);
+        double d = 0.0;
+#pragma unroll 4
+        for (int n = nlo + lane; n < nhi; n += 32) d = fma(xs[ks + n], __ldg(xj + n), d);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        if (lane == 0) se[warp] = d;
+    }
+    __syncthreads();
+    if (tid != 0) return;
+    double best = 0.0;
+#pragma unroll
+    for (int sl = 0; sl < XV_SL; ++sl) best += sp[sl];
+    int bl = cd[0];
+    unsigned long long ncand = 1;
+    for (int s_ = 1; s_ < XF_KC && cd[s_] != INT_MIN; ++s_) {
+        const double d = se[s_ - 1];
+        const int ks = cd[s_];
+        if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
+        ++ncand;
+    }
+    const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
+    const double c = best / sqrt(Ei * Ej);
+    const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+    g.lag[item] = bl;
+    if (g.cmax) g.cmax[item] = c;
+    atomicAdd(g.stat, ncand);
+    const float ee = fabsf((float)(c - (double)g.sval[it]));
+    if (!(ee <= 0.25f * XF_TAU32)) {
+        g.flag_list[atomicAdd(g.flag_count, 1)] = (int)item;
+        atomicAdd(g.stat + 1, 1ULL);
+    } else {
+        atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(ee));
     }
 }
 
@@ -1004,7 +1072,12 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         NBLS_CHECK(ensure(ctx, ctx->cand, (size_t)wb * P * XF_KC * sizeof(int32_t)));
         NBLS_CHECK(ensure(ctx, ctx->sval, (size_t)wb * P * sizeof(float)));
     }
-    if (pa) NBLS_CHECK(ensure(ctx, ctx->wfail, (size_t)wb * 2 * sizeof(int)));
+    // stage A -> B bookkeeping: [0] failing-pair counter, [1 .. wb*P] failing-pair items, then [wb] window list
+    if (pa) {
+        NBLS_CHECK(ensure(ctx, ctx->wfail, ((size_t)wb * P + wb + 4) * sizeof(int)));
+        NBLS_CUDA(cudaFuncSetAttribute(xf_verify_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)((size_t)N * sizeof(double))));
+    }
     for (const XfPlan* q : {pl, pa}) {
         if (!q) continue;
         NBLS_CUDA(cudaFuncSetAttribute(q->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q->smem));
@@ -1024,99 +1097,88 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     a.sval = (float*)ctx->sval.p;
     a.stat = (unsigned long long*)ctx->xstat.p;
     a.lag_dead = -lag_full;
-    a.wfail = (int*)ctx->wfail.p;
-    int* dwlist = a.wfail ? a.wfail + wb : nullptr;
-    std::vector<int> hfail, hlist, hlistA;
-    const bool use_probe = pa && !getenv("NBLS_NO_PROBE");
-    const int probe_pp = getenv("NBLS_PROBE_PP") ? std::max(1, atoi(getenv("NBLS_PROBE_PP"))) : 2;
+    a.pf_count = (int*)ctx->wfail.p;
+    a.pf_list = a.pf_count ? a.pf_count + 4 : nullptr;
+    int* dwlist = a.pf_list ? a.pf_list + (size_t)wb * P : nullptr;
+    std::vector<int> hitems, hwin;
 
+    // undecided arg-maxima are settled by the time-domain kernel (normally an empty list)
+    auto settle = [&]() -> int {
+        return xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
+                                 ctx->sm_count * 2);
+    };
     // one pass of spectra -> pair -> (verify) -> time-domain list over the windows described by `a`
-    auto pass = [&](const XfPlan* q, bool with_spectra) -> int {
+    auto pass = [&](const XfPlan* q) -> int {
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
-        if (with_spectra) {
-            q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
-            NBLS_CUDA(cudaGetLastError());
-            ctx->launches += 1;
-        }
+        q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
         q->pair<<<(unsigned)(a.wn * npp), q->threads, q->smem, ctx->stream>>>(a);
         NBLS_CUDA(cudaGetLastError());
-        ctx->launches += 1;
+        ctx->launches += 2;
         if (fp32) {
             const int nib = (C - 1 + ib - 1) / ib;
             verify<<<(unsigned)(a.wn * nib), vnw * 32, vsmem, ctx->stream>>>(a);
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 1;
         }
-        // undecided arg-maxima are settled by the time-domain kernel (normally an empty list)
-        return xcorr_direct_band(ctx, yband, ldy, C, N, hop, first, W, max_lag, lag, cmax, a.flag_list, a.flag_count,
-                                 ctx->sm_count * 2);
+        return settle();
     };
-    int64_t n_redo = 0;
+    int64_t n_redo = 0, n_redo_pairs = 0;
     for (int w0 = 0; w0 < W; w0 += wb) {
         const int wn = std::min(wb, W - w0);
-        a.w0 = w0;
-        if (pa) {
-            // stage A: |lag| <= k0 with the shorter transform, plus the proof that nothing beyond k0 can win
-            a.wn = wn; a.wlist = nullptr;
-            a.k0 = std::min(pa->L - N, N - 1); a.lag_max = a.k0;
-            a.SP = pa->L / 2 + 1; a.tw = twa;
-            NBLS_CUDA(cudaMemsetAsync(a.wfail, 0, (size_t)wn * sizeof(int), ctx->stream));
-            hfail.resize(wn);
-            hlist.clear();
-            if (use_probe) {
-                // probe: spectra of the whole batch, then two pair-pairs per window decide which windows cannot pass
-                pa->spectra<<<(unsigned)(wn * ncp), pa->threads, pa->smem, ctx->stream>>>(a);
-                NBLS_CUDA(cudaGetLastError());
-                a.probe = 1; a.npp_run = std::min(probe_pp, npp);
-                pa->pair<<<(unsigned)(wn * a.npp_run), pa->threads, pa->smem, ctx->stream>>>(a);
-                NBLS_CUDA(cudaGetLastError());
-                a.probe = 0; a.npp_run = 0;
-                ctx->launches += 2;
-                NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost,
-                                          ctx->stream));
-                NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-                hlistA.clear();
-                for (int i = 0; i < wn; ++i) (hfail[i] ? hlist : hlistA).push_back(w0 + i);
-                if (!hlistA.empty()) {
-                    NBLS_CUDA(cudaMemsetAsync(a.wfail, 0, (size_t)wn * sizeof(int), ctx->stream));
-                    NBLS_CUDA(cudaMemcpyAsync(dwlist, hlistA.data(), hlistA.size() * sizeof(int), cudaMemcpyHostToDevice,
-                                              ctx->stream));
-                    a.wn = (int)hlistA.size(); a.wlist = dwlist; a.spec_by_win = 1;
-                    NBLS_CHECK(pass(pa, false));
-                    a.spec_by_win = 0;
-                    NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, hlistA.size() * sizeof(int), cudaMemcpyDeviceToHost,
-                                              ctx->stream));
-                    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));   // also: hlistA is pageable and reused
-                    for (size_t i = 0; i < hlistA.size(); ++i)
-                        if (hfail[i]) hlist.push_back(hlistA[i]);
-                    std::sort(hlist.begin(), hlist.end());
-                }
-            } else {
-                NBLS_CHECK(pass(pa, true));
-                NBLS_CUDA(cudaMemcpyAsync(hfail.data(), a.wfail, (size_t)wn * sizeof(int), cudaMemcpyDeviceToHost,
-                                          ctx->stream));
-                NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-                for (int i = 0; i < wn; ++i)
-                    if (hfail[i]) hlist.push_back(w0 + i);
-            }
-            n_redo += (int64_t)hlist.size();
-            if (hlist.empty()) continue;
-            // stage B: the windows without a proof, over all lags
-            NBLS_CUDA(cudaMemcpyAsync(dwlist, hlist.data(), hlist.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-            NBLS_CUDA(cudaStreamSynchronize(ctx->stream));     // hlist is pageable and reused
-            a.wn = (int)hlist.size(); a.wlist = dwlist;
-        } else {
-            a.wn = wn; a.wlist = nullptr;
+        a.w0 = w0; a.wn = wn; a.wlist = nullptr; a.items = nullptr; a.n_items = 0;
+        if (!pa) {
+            a.k0 = -1; a.lag_max = lag_full;
+            a.SP = SP; a.tw = tw;
+            NBLS_CHECK(pass(pl));
+            continue;
         }
+        // stage A: |lag| <= k0 with the shorter transform, plus the proof per pair-window that nothing beyond k0 can win
+        a.k0 = std::min(pa->L - N, N - 1); a.lag_max = a.k0;
+        a.SP = pa->L / 2 + 1; a.tw = twa;
+        NBLS_CUDA(cudaMemsetAsync(a.pf_count, 0, sizeof(int), ctx->stream));
+        NBLS_CHECK(pass(pa));
+        int nfail = 0;
+        NBLS_CUDA(cudaMemcpyAsync(&nfail, a.pf_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (nfail == 0) continue;
+        // stage B: the pair-windows without a proof, over all lags.  The list is sorted so that the pairing of items in
+        // the packed transforms (and with it every FP32 value) does not depend on the order the atomics ran in.
+        hitems.resize(nfail);
+        NBLS_CUDA(cudaMemcpyAsync(hitems.data(), a.pf_list, (size_t)nfail * sizeof(int), cudaMemcpyDeviceToHost,
+                                  ctx->stream));
+        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+        std::sort(hitems.begin(), hitems.end());
+        hwin.clear();
+        for (int it : hitems) {
+            const int w = w0 + it / P;
+            if (hwin.empty() || hwin.back() != w) hwin.push_back(w);
+        }
+        n_redo += (int64_t)hwin.size();
+        n_redo_pairs += nfail;
+        NBLS_CUDA(cudaMemcpyAsync(a.pf_list, hitems.data(), (size_t)nfail * sizeof(int), cudaMemcpyHostToDevice,
+                                  ctx->stream));
+        NBLS_CUDA(cudaMemcpyAsync(dwlist, hwin.data(), hwin.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));     // both host lists are pageable and reused
         a.k0 = -1; a.lag_max = lag_full;
         a.SP = SP; a.tw = tw;
-        NBLS_CHECK(pass(pl, true));
+        NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
+        a.wn = (int)hwin.size(); a.wlist = dwlist;
+        pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        a.wlist = nullptr; a.items = a.pf_list; a.n_items = nfail;
+        pl->pair<<<(unsigned)((nfail + 1) / 2), pl->threads, pl->smem, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        xf_verify_items_kernel<<<(unsigned)nfail, XV_SL * 32, (size_t)N * sizeof(double), ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 3;
+        NBLS_CHECK(settle());
     }
     if (pa) {
         ctx->ts_windows += W;
         ctx->ts_redone += n_redo;
-        // a band where most windows had to be redone: leave the next three bands to the single-stage search
-        if (n_redo * 2 > (int64_t)W) ctx->ts_skip = 3;
+        // a band where most pair-windows had to be redone: leave the next three bands to the single-stage search
+        if (n_redo_pairs * 2 > (int64_t)W * P) ctx->ts_skip = 3;
     }
     return NBLS_OK;
 }
