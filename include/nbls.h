@@ -113,9 +113,10 @@ int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain,
 
 /* Two-stage lag search of NBLS_XCORR_AUTO (all 2N-1 lags requested, FP32 screen): stage A searches |lag| <= k0 with a
  * shorter transform and proves for every pair-window - Cauchy-Schwarz over the partial energies of the two windows - that no
- * lag beyond k0 can reach the maximum found; windows without a proof are redone over all lags, so the result is the arg-max
- * over all 2N-1 lags either way.  A band where most windows needed the second stage switches the next three bands to the
- * single-stage search.  Returns the windows searched in two stages and those redone since creation / the last reset. */
+ * lag beyond k0 can reach the maximum found; pair-windows without a proof are redone over all lags, so the result is the
+ * arg-max over all 2N-1 lags either way.  A band where most pair-windows needed the second stage switches the next three
+ * bands to the single-stage search.  Returns the windows searched in two stages and those that held at least one redone
+ * pair-window, since creation / the last reset. */
 int nbls_xcorr_two_stage_stats(nbls_ctx* ctx, int64_t* n_windows, int64_t* n_redone, int32_t reset);
 
 /* ---- K3: per-window statistics and slowness solve ---------------------------------- */

@@ -221,6 +221,37 @@ def test_xcorr_fft_every_transform_length(eng, n, method):
     assert np.array_equal(lag2, ref2)
 
 
+@pytest.mark.parametrize("n", [1200, 3000, 4400])
+def test_two_stage_redoes_single_pair_windows(eng, n):
+    """AUTO's two-stage search with pair-windows on both sides of the Cauchy-Schwarz proof: most channels carry the same
+    signal at small lags (stage A proves them), one channel is delayed far beyond stage A's lag bound, one is pure noise
+    and one is dead, so stage B runs in item mode on a ragged list of pair-windows (odd counts, items of different windows
+    sharing a packed transform).  Lags must equal the time-domain oracle's bit for bit; AUTO's cmax must agree with the
+    single-stage FP32 path's to the last bits (only the window energies are summed by kernels of different widths)."""
+    rng = np.random.default_rng(n + 1)
+    c, count = 7, 5
+    hop = n // 2
+    t = n + hop * (count - 1)
+    far = int(0.45 * n)                        # beyond stage A's lag bound k0 = L_A - N (336 / 1096 / 1744 here)
+    s = rng.standard_normal(t + far + 64)
+    x = np.stack([s[far + 2 * k:far + 2 * k + t] + 0.2 * rng.standard_normal(t) for k in range(c)])
+    x[3] = s[:t] + 0.2 * rng.standard_normal(t)          # delayed by `far` samples against the others
+    x[4] = rng.standard_normal(t)                        # incoherent
+    x[5] = 0.0                                           # dead channel: NaN cmax, lag -(N-1)
+    x[6, hop:hop + n // 3] = 0.0                          # a gap in one channel of the middle windows
+    ref_lag, ref_cmax = _oracle_xcorr(x, n, hop, count)
+    eng.xcorr_stats(reset=True)
+    lag, cmax = eng.xcorr(x[None], [n], [hop], [count], method=_capi.XCORR_AUTO)
+    st = eng.xcorr_stats(reset=True)
+    assert np.array_equal(lag, ref_lag)
+    assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-12, equal_nan=True)
+    assert st["two_stage_windows"] == count and st["two_stage_redone"] == count
+    assert np.abs(lag).max() >= far - 16                 # the far lags were found (only stage B can see them)
+    lag1, cmax1 = eng.xcorr(x[None], [n], [hop], [count], method=_capi.XCORR_FFT32)
+    assert np.array_equal(lag, lag1)
+    assert np.allclose(cmax, cmax1, rtol=0, atol=1e-14, equal_nan=True)
+
+
 def test_cheby1_branch_matches_reference(eng):
     """FILTER_TYPE='cheby1' (helpers.py:129-137 of the reference: one causal sosfilt pass, then the 1 % taper) through
     the package's filter_data on the GPU, against samples the unmodified reference produced (tests/golden/helpers.npz)."""
