@@ -243,7 +243,16 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     V* Xa = static_cast<V*>(g.spec) + ((int64_t)wl * g.C + ca) * g.SP;
     V* Xb = static_cast<V*>(g.spec) + ((int64_t)wl * g.C + cb) * g.SP;
     constexpr F half = (F)0.5;
-    for (int f = tid; f <= S::L / 2; f += T) {
+    // Consecutive f sit R2 rows apart in the in-place layout (pos(): the row is led by f % R1), which is a multiple of 32
+    // banks.  A warp therefore takes A consecutive f (one full 32-byte sector of each spectrum) times 32/A values of
+    // (f / R1) % R2, which are one row apart: A-way instead of R1-way bank conflicts, sectors still written whole.
+    constexpr int A = S::R1 % 4 == 0 ? 4 : (S::R1 % 2 == 0 ? 2 : 1), B = 32 / A;
+    constexpr int NJ = (S::L / 2 + 1 + S::R1 * B - 1) / (S::R1 * B);
+    const int la = lane % A, lb = lane / A;
+    for (int tile = warp; tile < (S::R1 / A) * NJ; tile += T / 32) {
+        const int i = tile % (S::R1 / A), j = tile / (S::R1 / A);
+        const int f = A * i + la + S::R1 * (B * j + lb);
+        if (f > S::L / 2) continue;
         const V yf = sm[S::pos(f)];
         const V ym = sm[S::pos(f == 0 ? 0 : S::L - f)];
         Xa[f] = mk2(half * (yf.x + ym.x), half * (ym.y - yf.y));
