@@ -10,7 +10,8 @@ N > 1 (torchrun): the record is N x 24 h long and is sharded by time segment wit
 one rank per GPU (weak scaling); the per-window result arrays are gathered with NCCL.
 
 `value`   = estimates / device time with the record resident in HBM (CUDA events on libnbls' stream).
-`e2e`     = the same through the host-buffer C-ABI call nbls_run_host (pinned H2D + path + D2H).
+`e2e`     = the same through the host-buffer C-ABI call nbls_run_host (pinned H2D + path + D2H), by default with two
+            records in flight on two contexts (`--e2e-in-flight 1` = strictly one after the other).
 `roofline`= the dominant kernel (cross-correlation, FP64-FMA bound) against the DFMA peak measured
             in this run; `roofline_filter` = the HBM-bound filter kernels against MEASURED_PEAKS.json.
 `cpu_baseline` / --impl reference = the reference's algorithm (oracle port: the same numpy/scipy calls,
@@ -48,6 +49,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-min", type=float, default=3.0, help="minutes of record for the CPU legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--e2e-in-flight", type=int, default=2,
+                    help="records in flight in the e2e leg (own context each; 1 = strictly one after the other)")
     return ap.parse_args()
 
 
@@ -245,20 +248,60 @@ def run_b200(args):
     value = e_total / (ms_per_step * 1e-3)
 
     # ---- e2e: host buffers through nbls_run_host, every step H2D + D2H ----
+    # `--e2e-in-flight n` (default 2) keeps n records in flight, each on its own context (own stream and workspace): the
+    # H2D copy and the host-side waits of record k+1 overlap the kernels of record k, as a caller working through a
+    # queue of records would run it.  Every step still copies its input from pinned host memory and its results back.
     e2e = None
     if not args.no_e2e:
-        eng.run(plan, x_host, res)                            # one warm-up (buffers grow once)
+        import threading
+        nfl = max(1, min(args.e2e_in_flight, args.steps))
+        engs = [eng] + [Engine(local_rank) for _ in range(nfl - 1)]
+        ress = [res] + [Results(plan, pinned=True, want_cmax=False) for _ in range(nfl - 1)]
+        for e_, r_ in zip(engs, ress):
+            e_.run(plan, x_host, r_)                          # one warm-up each (buffers grow once)
+        for r_ in ress[1:]:                                   # every context computes the same bits
+            assert np.array_equal(r_.lag, res.lag) and np.array_equal(r_.vel, res.vel, equal_nan=True)
         barrier()
+        done = [threading.Event() for _ in range(args.steps)]
+        gathered = [threading.Event() for _ in range(args.steps)]
+        step_ms = [0.0] * args.steps
+        errors = []
+
+        def worker(i):
+            try:
+                for k in range(i, args.steps, nfl):
+                    if k - nfl >= 0:
+                        gathered[k - nfl].wait()              # the results buffer of this context is free again
+                    engs[i].run(plan, x_host, ress[i])
+                    step_ms[k] = engs[i].timings()["total"]
+                    done[k].set()
+            except BaseException as exc:                      # noqa: BLE001 - re-raised in the main thread
+                errors.append(exc)
+                for ev in done:
+                    ev.set()
+
         w0 = time.perf_counter()
-        e_ms = 0.0
-        for _ in range(args.steps):
-            eng.run(plan, x_host, res)
-            e_ms += eng.timings()["total"]
+        threads = [threading.Thread(target=worker, args=(i,)) for i in range(nfl)]
+        for th in threads:
+            th.start()
+        for k in range(args.steps):
+            done[k].wait()
+            if errors:
+                break
             if dist is not None:
-                gather_results({k: getattr(res, k)[:e_local] for k in ("mdccm", "vel", "baz", "sigma_tau")},
+                r_ = ress[k % nfl]
+                gather_results({kk: getattr(r_, kk)[:e_local] for kk in ("mdccm", "vel", "baz", "sigma_tau")},
                                plan.win_count)
+            gathered[k].set()
+        for ev in gathered:
+            ev.set()
+        for th in threads:
+            th.join()
+        if errors:
+            raise errors[0]
         barrier()
         e_wall = (time.perf_counter() - w0) * 1e3
+        e_ms = sum(step_ms)
         if dist is not None:
             import torch
             tt = torch.tensor([e_wall], dtype=torch.float64, device="cuda")
@@ -266,7 +309,8 @@ def run_b200(args):
             e_wall = float(tt[0])
         e2e = {"value": e_total / (e_wall / args.steps * 1e-3), "unit": "estimates/s",
                "h2d_bytes_per_step": int(x_host.nbytes) * world, "d2h_bytes_per_step": int(res.nbytes()) * world,
-               "ms_per_step_wall": e_wall / args.steps, "ms_per_step_device": e_ms / args.steps}
+               "ms_per_step_wall": e_wall / args.steps, "ms_record_latency_device": e_ms / args.steps,
+               "records_in_flight": nfl}
     return dict(j=j, plan=plan, world=world, rank=rank, value=value, ms_per_step=ms_per_step, wall_ms=wall_ms,
                 stage={k: v / args.steps for k, v in stage.items()}, clocks=clocks, launches=launches, e2e=e2e,
                 fp64_peak=fp64_peak, fp32_peak=fp32_peak, xstats=xstats, e_total=e_total, e_local=e_local, shard=shard, sos=sos, win_len=win_len,
@@ -294,7 +338,9 @@ def config_block(j, world, args, extra=None):
                      f"{j['winlen_list'][-1]:g} s, 50% overlap, butter order {j['filter_order']} zero-phase",
          "sharding": "1 GPU" if world == 1 else f"time segments with filter halos over {world} GPUs, record = {world} x {j['hours_per_gpu']:g} h",
          "l2": "inputs larger than L2 (record and filtered bands are GB-sized)", "xcorr_method": args.method,
-         "max_lag": args.max_lag}
+         "max_lag": args.max_lag,
+         "e2e": (f"{max(1, min(args.e2e_in_flight, args.steps))} record(s) in flight, one context each; every step copies its "
+                 "input from pinned host memory and its results back inside the timed region")}
     if extra:
         c.update(extra)
     return c

@@ -49,6 +49,19 @@ enum { EV_START = 0, EV_H2D, EV_FILTER, EV_XCORR, EV_SOLVE, EV_D2H, EV_COUNT };
 
 }  // namespace nbls
 
+namespace nbls {
+// Lets a kernel use the device's whole opt-in shared memory.  Always the same value for a given kernel, so contexts working
+// on different jobs from different host threads cannot lower each other's limit between this call and the launch (the
+// attribute is per function, not per context).
+template <class K>
+inline cudaError_t allow_max_dynamic_smem(K fn, size_t smem_optin) {
+    cudaFuncAttributes at;
+    cudaError_t e = cudaFuncGetAttributes(&at, fn);
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem_optin - at.sharedSizeBytes));
+}
+}  // namespace nbls
+
 struct nbls_ctx {
     int device = 0;
     int sm_count = 0;

@@ -105,7 +105,7 @@ int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int3
     a.slow = out->slowness;
     const size_t smem = (size_t)OLS_WARPS * P * sizeof(double);
     NBLS_REQUIRE(smem <= ctx->smem_optin, "nbls_solve: too many pairs (%d)", P);
-    NBLS_CUDA(cudaFuncSetAttribute(stats_ols_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NBLS_CUDA(allow_max_dynamic_smem(stats_ols_kernel, ctx->smem_optin));
     const int64_t want = (nwin + OLS_WARPS - 1) / OLS_WARPS;
     const int grid = (int)std::min<int64_t>(want, (int64_t)ctx->sm_count * 16);
     stats_ols_kernel<<<grid, OLS_WARPS * 32, smem, ctx->stream>>>(a);

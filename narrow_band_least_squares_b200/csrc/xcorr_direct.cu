@@ -222,7 +222,7 @@ int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, in
                   ctx->smem_optin - 1024);
         return NBLS_ERR_UNSUPPORTED;
     }
-    NBLS_CUDA(cudaFuncSetAttribute(xcorr_direct_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NBLS_CUDA(allow_max_dynamic_smem(xcorr_direct_kernel, ctx->smem_optin));
     const int64_t nblocks = list ? std::min<int64_t>((int64_t)W * P, std::max(1, grid_cap)) : (int64_t)W * P;
     NBLS_REQUIRE(nblocks < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld", (long long)nblocks);
     xcorr_direct_kernel<<<(unsigned)nblocks, nwarps * 32, smem, ctx->stream>>>(a);

@@ -1061,7 +1061,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         verify = pick_verify(N, C, ctx->smem_optin, &ib, &vnw);
         NBLS_REQUIRE(verify, "nbls_xcorr(fft32): a window of %d samples does not fit in shared memory", N);
         vsmem = verify_smem(ib, N, C);
-        NBLS_CUDA(cudaFuncSetAttribute(verify, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)vsmem));
+        NBLS_CUDA(allow_max_dynamic_smem(verify, ctx->smem_optin));
     }
     // windows per batch: spectra workspace bounded (they are re-read from L2 window by window)
     const int SP = pl->L / 2 + 1;
@@ -1084,8 +1084,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     // stage A -> B bookkeeping: [0] failing-pair counter, [1 .. wb*P] failing-pair items, then [wb] window list
     if (pa) {
         NBLS_CHECK(ensure(ctx, ctx->wfail, ((size_t)wb * P + wb + 4) * sizeof(int)));
-        NBLS_CUDA(cudaFuncSetAttribute(xf_verify_items_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)((size_t)N * sizeof(double))));
+        NBLS_CUDA(allow_max_dynamic_smem(xf_verify_items_kernel, ctx->smem_optin));
     }
     for (const XfPlan* q : {pl, pa}) {
         if (!q) continue;
