@@ -252,6 +252,44 @@ def test_two_stage_redoes_single_pair_windows(eng, n):
     assert np.allclose(cmax, cmax1, rtol=0, atol=1e-14, equal_nan=True)
 
 
+def test_two_contexts_run_different_jobs_concurrently(eng):
+    """Two contexts on one GPU, driven from two host threads with jobs of very different shared-memory needs (the
+    two-records-in-flight mode of bench.py's e2e leg): each must return exactly what it returns alone."""
+    import threading
+    from narrow_band_least_squares_b200.engine import Engine
+    rng = np.random.default_rng(77)
+    jobs = []
+    for n, c in ((3000, 6), (700, 9)):
+        hop, count = n // 2, 6
+        t = n + hop * (count - 1)
+        s = rng.standard_normal(t + 64)
+        x = np.stack([s[2 * k:2 * k + t] + 0.4 * rng.standard_normal(t) for k in range(c)])
+        x[c - 1] = rng.standard_normal(t)                # an incoherent channel: stage B (item mode) has work
+        jobs.append((x[None], [n], [hop], [count]))
+    alone = [eng.xcorr(*j, method=_capi.XCORR_AUTO) for j in jobs]
+    eng2 = Engine(0)
+    try:
+        engines, out, errs = (eng, eng2), [None, None], []
+
+        def work(i):
+            try:
+                for _ in range(8):
+                    out[i] = engines[i].xcorr(*jobs[i], method=_capi.XCORR_AUTO)
+                    assert np.array_equal(out[i][0], alone[i][0])
+                    assert np.array_equal(out[i][1], alone[i][1], equal_nan=True)
+            except BaseException as exc:                 # noqa: BLE001 - reported by the main thread
+                errs.append(exc)
+
+        th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+        for t_ in th:
+            t_.start()
+        for t_ in th:
+            t_.join()
+        assert not errs, errs
+    finally:
+        eng2.close()
+
+
 def test_cheby1_branch_matches_reference(eng):
     """FILTER_TYPE='cheby1' (helpers.py:129-137 of the reference: one causal sosfilt pass, then the 1 % taper) through
     the package's filter_data on the GPU, against samples the unmodified reference produced (tests/golden/helpers.npz)."""
