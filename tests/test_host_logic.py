@@ -288,3 +288,30 @@ def test_results_txtfile_is_byte_identical_to_reference(tmp_path):
     for k, v in zip(("vel", "baz", "mdccm", "t", "freqlist", "ncl"), back[:6]):
         assert np.array_equal(np.asarray(v, dtype=np.float64), g[f"txt_back_{k}"], equal_nan=True), k
     assert np.array_equal(np.array(back[6:9], dtype=np.float64), g["txt_back_scalars"])
+
+
+def test_remove_elements_edits_the_callers_lists_like_the_reference():
+    """lts_data_class.py:34-40: the listed elements (python numbering, any order) leave the caller's stream and coordinate
+    lists in place; the data matrix, element names and co-array are built from what remains."""
+    from narrow_band_least_squares_b200.ltsva import DataBin
+    from narrow_band_least_squares_b200.stream import stream_from_array
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((6, 4000))
+    st = stream_from_array(x, 100.0, stations=[f"I53H{k + 1}" for k in range(6)])
+    lat = [64.0 + 1e-3 * k for k in range(6)]
+    lon = [-147.0 - 2e-3 * k * k for k in range(6)]
+    lat_all, lon_all = list(lat), list(lon)
+    d = DataBin(10.0, 0.5, 1.0)
+    d.build_data_arrays(st, lat, lon, remove_elements=[4, 1])
+    keep = [0, 2, 3, 5]
+    assert len(st) == 4 and lat == [lat_all[k] for k in keep] and lon == [lon_all[k] for k in keep]
+    assert d.nchans == 4 and d.element_names == [f"{k + 1:02d}" for k in keep]      # Trace.stats.location
+    assert np.array_equal(d.data_ct, x[keep])
+    ref = DataBin(10.0, 0.5, 1.0)
+    ref.build_data_arrays(stream_from_array(x[keep], 100.0, stations=[f"I53H{k + 1}" for k in keep]),
+                          [lat_all[k] for k in keep], [lon_all[k] for k in keep])
+    assert np.array_equal(d.rij, ref.rij) and d.nits == ref.nits == (4000 - 1000 + 499) // 500
+    with pytest.raises(RuntimeError):                    # fewer than 3 elements left (lts_data_class.py:76-80)
+        DataBin(10.0, 0.5, 1.0).build_data_arrays(stream_from_array(x[:4], 100.0), lat_all[:4], lon_all[:4],
+                                                   remove_elements=[0, 1])
+
