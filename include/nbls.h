@@ -19,8 +19,10 @@
  * device memory owned by the caller; every other pointer is host memory and is read
  * before the call returns.  All calls are ordered on the context's stream and
  * return after enqueueing unless stated; nbls_synchronize() waits.  Return value 0 = OK,
- * otherwise an NBLS_ERR_* code and nbls_last_error() describes it.  One context per GPU;
- * a context is not thread-safe.  There is no CPU fallback: without a CUDA device
+ * otherwise an NBLS_ERR_* code and nbls_last_error() describes it (per host thread).  A
+ * context owns one stream and its workspaces and is driven by one host thread at a time;
+ * several contexts on one GPU are independent and may run concurrently from different
+ * threads (e.g. two records in flight).  There is no CPU fallback: without a CUDA device
  * nbls_create fails.
  */
 #ifndef NBLS_H_
