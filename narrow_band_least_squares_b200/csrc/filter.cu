@@ -235,24 +235,67 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
 }
 
 // phase 2: state[k] (chunk end states from zero) -> state[k] (true chunk start states)
-__global__ void carry_kernel(double* state, const double* ML, int B, int C, int nchunks, int S2, int reverse) {
+template <int S2>
+__global__ void carry_kernel(double* state, const double* ML, int B, int C, int nchunks, int reverse) {
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
     if (id >= B * C) return;
     const int band = id / C;
-    const double* M = ML + (int64_t)band * S2 * S2;
     double* st = state + (int64_t)id * nchunks * S2;
-    double s[2 * NBLS_MAX_SECTIONS], e[2 * NBLS_MAX_SECTIONS], t[2 * NBLS_MAX_SECTIONS];
+    // A^L of the band: in registers for up to 3 sections, otherwise read through L1 every step
+    constexpr bool MREG = S2 <= 6;
+    const double* Mg = ML + (int64_t)band * S2 * S2;
+    double M[MREG ? S2 * S2 : 1], s[S2];
+    if constexpr (MREG) {
+#pragma unroll
+        for (int i = 0; i < S2 * S2; ++i) M[i] = Mg[i];
+    }
+#pragma unroll
     for (int i = 0; i < S2; ++i) s[i] = 0.0;
-    for (int step = 0; step < nchunks; ++step) {
-        const int k = reverse ? nchunks - 1 - step : step;
-        double* p = st + (int64_t)k * S2;
-        for (int i = 0; i < S2; ++i) { e[i] = p[i]; p[i] = s[i]; }
-        for (int i = 0; i < S2; ++i) {
-            double acc = e[i];
-            for (int j = 0; j < S2; ++j) acc = fma(M[i * S2 + j], s[j], acc);
-            t[i] = acc;
+    // the chunk end states e[k] do not depend on the recurrence: fetch PF of them ahead of the serial chain
+    constexpr int PF = S2 <= 4 ? 8 : (S2 <= 8 ? 4 : 2);      // e[PF][S2] stays within 32 doubles
+    for (int step0 = 0; step0 < nchunks; step0 += PF) {
+        double e[PF][S2];
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int step = step0 + u;
+            if (step < nchunks) {
+                const double* p = st + (int64_t)(reverse ? nchunks - 1 - step : step) * S2;
+#pragma unroll
+                for (int i = 0; i < S2; ++i) e[u][i] = p[i];
+            }
         }
-        for (int i = 0; i < S2; ++i) s[i] = t[i];
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int step = step0 + u;
+            if (step < nchunks) {
+                double* p = st + (int64_t)(reverse ? nchunks - 1 - step : step) * S2;
+                double t[S2];
+#pragma unroll
+                for (int i = 0; i < S2; ++i) {
+                    p[i] = s[i];
+                    double acc = e[u][i];
+#pragma unroll
+                    for (int j = 0; j < S2; ++j) acc = fma(MREG ? M[i * S2 + j] : __ldg(Mg + i * S2 + j), s[j], acc);
+                    t[i] = acc;
+                }
+#pragma unroll
+                for (int i = 0; i < S2; ++i) s[i] = t[i];
+            }
+        }
+    }
+}
+
+typedef void (*carry_fn)(double*, const double*, int, int, int, int);
+static carry_fn pick_carry(int S) {
+    switch (S) {
+        case 1: return carry_kernel<2>;
+        case 2: return carry_kernel<4>;
+        case 3: return carry_kernel<6>;
+        case 4: return carry_kernel<8>;
+        case 5: return carry_kernel<10>;
+        case 6: return carry_kernel<12>;
+        case 7: return carry_kernel<14>;
+        default: return carry_kernel<16>;
     }
 }
 
@@ -428,7 +471,7 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
             a.out = nullptr; a.proc_tiles = dproc; a.state_in = nullptr; a.state_out = dstate;
             fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
             NBLS_CUDA(cudaGetLastError());
-            carry_kernel<<<(B * C + 127) / 128, 128, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, S2, rev ? 1 : 0);
+            pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, rev ? 1 : 0);
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 2;
         }
