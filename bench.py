@@ -431,12 +431,12 @@ def main():
                                   "two-stage search executes less (xcorr_stats.two_stage_*), so 'achieved' is "
                                   "algorithmic work per second, not executed flop/s") if args.method == "auto" else None,
                          "fp64_peak": r["fp64_peak"], "fp32_peak": r["fp32_peak"]},
-            "roofline_filter": {"kernel": "biquad_chunk_kernel x4 + carry_kernel x2", "bound": "hbm", "achieved": fgb,
+            "roofline_filter": {"kernel": "biquad_state_shared_kernel + biquad_chunk_kernel x3 + carry_kernel x2", "bound": "hbm", "achieved": fgb,
                                 "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": (fgb / peaks["hbm_gbs"]) if fgb else None,
                                 "peak_source": peak_src, "algorithmic_bytes": filt_bytes,
                                 # dram__bytes_read + write of the six filter kernels, ncu capture of this workload at its
                                 # default length (profiles/r1_filter_24h_kernels.csv); not measured live
-                                "traffic": 134.7e9 if (args.workload == "c3" and args.hours is None and r["world"] == 1)
+                                "traffic": 122.8e9 if (args.workload == "c3" and args.hours is None and r["world"] == 1)
                                 else None}}
     try:
         st = r["xstats"]

@@ -23,6 +23,7 @@
 
 #include <algorithm>
 #include <complex>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
@@ -235,6 +236,155 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
 }
 
 // phase 2: state[k] (chunk end states from zero) -> state[k] (true chunk start states)
+// Phase 1 of the forward pass when every band reads the same rows (the raw record): one block per (32 chunks, channel)
+// moves each input tile ONCE through a block-wide cp.async ring and all bands take their chunk end states from it -
+// warp w runs bands w, w+FS_WARPS, ... of the tile, NA of them at a time with the sample loop outermost, so a lane
+// carries NA independent recurrences.  biquad_chunk_kernel would read the record once per band instead (its warps
+// reach the same samples milliseconds apart, far beyond the residency of a line in L2).  Needs proc_tiles to be
+// non-increasing over the band index (bands ordered by rising frequency), so that the active bands of a warp are a
+// prefix of its list; the host checks that.  Same arithmetic per band as biquad_warp<.., STATE_ONLY>.
+constexpr int FS_WARPS = 4;
+// bands [Q0, Q0 + NA) of the warp's list over one tile row
+template <int S, int NBW, int Q0, int NA>
+__device__ __forceinline__ void state_tile(const double* row, const double (*cf)[5], double (&z0)[NBW][S],
+                                           double (&z1)[NBW][S]) {
+    double b0[NA][S], b1[NA][S], b2[NA][S], a1[NA][S], a2[NA][S];
+#pragma unroll
+    for (int q = 0; q < NA; ++q)
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const double* c = cf[(Q0 + q) * S + s];
+            b0[q][s] = c[0]; b1[q][s] = c[1]; b2[q][s] = c[2]; a1[q][s] = c[3]; a2[q][s] = c[4];
+        }
+#pragma unroll 4
+    for (int j = 0; j < FT_TILE; ++j) {
+        const double xin = row[j];
+#pragma unroll
+        for (int q = 0; q < NA; ++q) {
+            double x = xin;
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const double y = fma(b0[q][s], x, z0[Q0 + q][s]);
+                z0[Q0 + q][s] = fma(b1[q][s], x, fma(-a1[q][s], y, z1[Q0 + q][s]));
+                z1[Q0 + q][s] = fma(b2[q][s], x, -(a2[q][s] * y));
+                x = y;
+            }
+        }
+    }
+}
+
+template <int S, int NBW>
+__global__ void __launch_bounds__(FS_WARPS * 32, 4) biquad_state_shared_kernel(FilterArgs a) {
+    extern __shared__ __align__(16) double smem[];
+    __shared__ double coef_sh[FS_WARPS][NBW * S][5];
+    __shared__ int first_sh[FS_WARPS][NBW];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int chan = blockIdx.y;
+    const int64_t chunk0 = (int64_t)blockIdx.x * 32;
+    const int ntiles = a.L / FT_TILE;
+    const double* in = a.in + (int64_t)chan * a.in_row;
+    // this warp's bands, their coefficients and first tiles; the block starts at the earliest first tile of all bands
+    if (lane < NBW) {
+        const int band = warp + lane * FS_WARPS;
+        first_sh[warp][lane] = band < a.B ? ntiles - min(ntiles, a.proc_tiles[band]) : ntiles;
+    }
+    for (int e = lane; e < NBW * S * 5; e += 32) {
+        const int q = e / (S * 5), r = e - q * (S * 5);
+        const int band = warp + q * FS_WARPS;
+        coef_sh[warp][q * S + r / 5][r % 5] = band < a.B ? a.coef[(int64_t)band * S * 5 + r] : 0.0;
+    }
+    __syncthreads();
+    int first = ntiles;
+#pragma unroll
+    for (int w = 0; w < FS_WARPS; ++w) first = min(first, first_sh[w][0]);
+    int myfirst[NBW];
+#pragma unroll
+    for (int q = 0; q < NBW; ++q) myfirst[q] = first_sh[warp][q];
+    const bool edge = (chunk0 + 32) * a.L > a.T;
+
+    // block-wide copy of tile i: 32 rows x FT_SEGS 16-byte pieces over FS_WARPS*32 threads
+    auto issue = [&](int i, int stage) {
+        double* tile = smem + stage * FT_TILE_DOUBLES;
+#pragma unroll
+        for (int q = 0; q < 32 * FT_SEGS / (FS_WARPS * 32); ++q) {
+            const int id = tid + q * FS_WARPS * 32;
+            const int r = id / FT_SEGS, seg = id - r * FT_SEGS;
+            const int64_t t = (chunk0 + r) * a.L + (int64_t)FT_TILE * i + seg * 2;
+            int bytes = 16;
+            if (edge) {
+                bytes = 0;
+                if (chunk0 + r < a.nchunks) {
+                    const int64_t left = a.T - t;
+                    bytes = left >= 2 ? 16 : (left == 1 ? 8 : 0);
+                }
+            }
+            cp_async16(tile + r * FT_ROW + seg * 2, bytes ? (const void*)(in + t) : (const void*)in, bytes);
+        }
+    };
+    double z0[NBW][S], z1[NBW][S];
+#pragma unroll
+    for (int q = 0; q < NBW; ++q)
+#pragma unroll
+        for (int s_ = 0; s_ < S; ++s_) { z0[q][s_] = 0.0; z1[q][s_] = 0.0; }
+
+#pragma unroll
+    for (int st = 0; st < FT_STAGES - 1; ++st) {
+        if (first + st < ntiles) issue(first + st, st);
+        cp_async_commit();
+    }
+    int stage = 0;
+    for (int i = first; i < ntiles; ++i) {
+        {
+            const int nxt = i + FT_STAGES - 1;
+            int nstage = stage + FT_STAGES - 1;
+            if (nstage >= FT_STAGES) nstage -= FT_STAGES;
+            if (nxt < ntiles) issue(nxt, nstage);
+            cp_async_commit();
+        }
+        cp_async_wait<FT_STAGES - 1>();
+        __syncthreads();
+        const double* row = smem + stage * FT_TILE_DOUBLES + lane * FT_ROW;
+        // active bands of this warp at tile i: a prefix of its list (proc_tiles does not increase with the band index)
+        int na = 0;
+#pragma unroll
+        for (int q = 0; q < NBW; ++q) na += (i >= myfirst[q]) ? 1 : 0;
+        // NA recurrences side by side; the z arrays of the first NA bands are the leading rows
+        // at most three recurrences side by side (their coefficients fill the registers), the rest in a second sweep
+        auto sweep = [&](auto q0, auto na_) {
+            constexpr int Q0 = decltype(q0)::value, NA = decltype(na_)::value;
+            if constexpr (Q0 + NA <= NBW) state_tile<S, NBW, Q0, NA>(row, coef_sh[warp], z0, z1);
+        };
+        using std::integral_constant;
+        switch (na) {
+            case 1: sweep(integral_constant<int, 0>{}, integral_constant<int, 1>{}); break;
+            case 2: sweep(integral_constant<int, 0>{}, integral_constant<int, 2>{}); break;
+            case 3: sweep(integral_constant<int, 0>{}, integral_constant<int, 3>{}); break;
+            case 4: sweep(integral_constant<int, 0>{}, integral_constant<int, 2>{});
+                    sweep(integral_constant<int, 2>{}, integral_constant<int, 2>{}); break;
+            case 5: sweep(integral_constant<int, 0>{}, integral_constant<int, 3>{});
+                    sweep(integral_constant<int, 3>{}, integral_constant<int, 2>{}); break;
+            case 6: sweep(integral_constant<int, 0>{}, integral_constant<int, 3>{});
+                    sweep(integral_constant<int, 3>{}, integral_constant<int, 3>{}); break;
+            default: break;
+        }
+        __syncthreads();          // every warp is done with this stage before the ring refills it
+        if (++stage == FT_STAGES) stage = 0;
+    }
+    cp_async_wait<0>();
+    const int64_t mychunk = chunk0 + lane;
+    if (mychunk < a.nchunks) {
+#pragma unroll
+        for (int q = 0; q < NBW; ++q) {
+            const int band = warp + q * FS_WARPS;
+            if (band < a.B) {
+                const int64_t sidx = (((int64_t)band * a.C + chan) * a.nchunks + mychunk) * (2 * S);
+#pragma unroll
+                for (int s_ = 0; s_ < S; ++s_) { a.state_out[sidx + 2 * s_] = z0[q][s_]; a.state_out[sidx + 2 * s_ + 1] = z1[q][s_]; }
+            }
+        }
+    }
+}
+
 template <int S2>
 __global__ void carry_kernel(double* state, const double* ML, int B, int C, int nchunks, int reverse) {
     const int id = blockIdx.x * blockDim.x + threadIdx.x;
@@ -282,6 +432,30 @@ __global__ void carry_kernel(double* state, const double* ML, int B, int C, int 
                 for (int i = 0; i < S2; ++i) s[i] = t[i];
             }
         }
+    }
+}
+
+typedef void (*state_fn)(FilterArgs);
+template <int S>
+static state_fn pick_state_nbw(int nbw) {
+    switch (nbw) {
+        case 1: return biquad_state_shared_kernel<S, 1>;
+        case 2: return biquad_state_shared_kernel<S, 2>;
+        case 3: return biquad_state_shared_kernel<S, 3>;
+        case 4: return biquad_state_shared_kernel<S, 4>;
+        case 5: return biquad_state_shared_kernel<S, 5>;
+        case 6: return biquad_state_shared_kernel<S, 6>;
+        default: return nullptr;
+    }
+}
+static state_fn pick_state(int S, int nbw) {
+    if (S * nbw > 10) return nullptr;      // more states than fit in 128 registers: the per-band kernel serves
+    switch (S) {
+        case 1: return pick_state_nbw<1>(nbw);
+        case 2: return pick_state_nbw<2>(nbw);
+        case 3: return pick_state_nbw<3>(nbw);
+        case 4: return pick_state_nbw<4>(nbw);
+        default: return nullptr;
     }
 }
 
@@ -461,6 +635,14 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         NBLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
 
+    // shared-read phase 1 of the forward pass: needs the bands' decay lengths to fall with the band index
+    state_fn shared_p1 = nullptr;
+    {
+        bool mono = true;
+        for (int b = 1; b < B; ++b) mono = mono && hproc[b] <= hproc[b - 1];
+        if (mono && nchunks > 1 && !getenv("NBLS_FILTER_NO_SHARED_P1"))
+            shared_p1 = pick_state(S, (B + FS_WARPS - 1) / FS_WARPS);
+    }
     auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
         chunk_fn fn = pick(S, rev);
         FilterArgs a;
@@ -469,7 +651,13 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         a.coef = dcoef; a.B = B; a.C = C; a.T = T; a.L = (int)L; a.nchunks = nchunks;
         if (nchunks > 1) {
             a.out = nullptr; a.proc_tiles = dproc; a.state_in = nullptr; a.state_out = dstate;
-            fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+            if (!rev && in_band == 0 && shared_p1) {
+                // every band reads the same record: one read of each tile for all bands
+                const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
+                shared_p1<<<dim3(grid.y, C), FS_WARPS * 32, smem1, ctx->stream>>>(a);
+            } else {
+                fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+            }
             NBLS_CUDA(cudaGetLastError());
             pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, rev ? 1 : 0);
             NBLS_CUDA(cudaGetLastError());
