@@ -55,6 +55,7 @@ struct FilterArgs {
     const double* taper_up;
     const double* taper_down;
     int64_t taper_len, g0, G;
+    int nsplit;                // biquad_state_shared_kernel: blockIdx.z = g takes bands g, g + nsplit, g + 2 nsplit, ...
 };
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc, int src_bytes) {
@@ -157,7 +158,7 @@ __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, i
                     // holds for phase 3 of a multi-chunk run (its start states come from that scan); a single-chunk
                     // run keeps scipy's unfused order below and stays bit-identical to sosfilt
                     const double y = fma(b0[s], x, z0[s]);
-                    z0[s] = fma(b1[s], x, fma(-a1[s], y, z1[s]));
+                    z0[s] = fma(-a1[s], y, fma(b1[s], x, z1[s]));   // b1 x + z1 is off the z0 -> y -> z0 chain
                     z1[s] = fma(b2[s], x, -(a2[s] * y));
                     x = y;
                 } else {
@@ -265,7 +266,8 @@ __device__ __forceinline__ void state_tile(const double* row, const double (*cf)
 #pragma unroll
             for (int s = 0; s < S; ++s) {
                 const double y = fma(b0[q][s], x, z0[Q0 + q][s]);
-                z0[Q0 + q][s] = fma(b1[q][s], x, fma(-a1[q][s], y, z1[Q0 + q][s]));
+                // b1 x + z1 does not wait for y: two dependent FMAs per sample on the z0 -> y -> z0 chain instead of three
+                z0[Q0 + q][s] = fma(-a1[q][s], y, fma(b1[q][s], x, z1[Q0 + q][s]));
                 z1[Q0 + q][s] = fma(b2[q][s], x, -(a2[q][s] * y));
                 x = y;
             }
@@ -284,13 +286,14 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 4) biquad_state_shared_kernel(F
     const int ntiles = a.L / FT_TILE;
     const double* in = a.in + (int64_t)chan * a.in_row;
     // this warp's bands, their coefficients and first tiles; the block starts at the earliest first tile of all bands
+    const int bsplit = blockIdx.z, nsplit = a.nsplit;
     if (lane < NBW) {
-        const int band = warp + lane * FS_WARPS;
+        const int band = bsplit + nsplit * (warp + lane * FS_WARPS);
         first_sh[warp][lane] = band < a.B ? ntiles - min(ntiles, a.proc_tiles[band]) : ntiles;
     }
     for (int e = lane; e < NBW * S * 5; e += 32) {
         const int q = e / (S * 5), r = e - q * (S * 5);
-        const int band = warp + q * FS_WARPS;
+        const int band = bsplit + nsplit * (warp + q * FS_WARPS);
         coef_sh[warp][q * S + r / 5][r % 5] = band < a.B ? a.coef[(int64_t)band * S * 5 + r] : 0.0;
     }
     __syncthreads();
@@ -375,7 +378,7 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 4) biquad_state_shared_kernel(F
     if (mychunk < a.nchunks) {
 #pragma unroll
         for (int q = 0; q < NBW; ++q) {
-            const int band = warp + q * FS_WARPS;
+            const int band = bsplit + nsplit * (warp + q * FS_WARPS);
             if (band < a.B) {
                 const int64_t sidx = (((int64_t)band * a.C + chan) * a.nchunks + mychunk) * (2 * S);
 #pragma unroll
@@ -636,12 +639,18 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     }
 
     // shared-read phase 1 of the forward pass: needs the bands' decay lengths to fall with the band index
+    // The bands are dealt to `nsplit` blocks per (32 chunks, channel) so that a warp carries at most three of them: a lane's
+    // recurrences are serial over the chunk, and the longest (lowest band, whole chunk) sets the kernel time.
     state_fn shared_p1 = nullptr;
+    int nsplit = 1;
     {
         bool mono = true;
         for (int b = 1; b < B; ++b) mono = mono && hproc[b] <= hproc[b - 1];
+        if (getenv("NBLS_FILTER_SPLIT")) nsplit = std::max(1, atoi(getenv("NBLS_FILTER_SPLIT")));
+        else nsplit = 1;
+        const int per_block = (B + nsplit - 1) / nsplit;
         if (mono && nchunks > 1 && !getenv("NBLS_FILTER_NO_SHARED_P1"))
-            shared_p1 = pick_state(S, (B + FS_WARPS - 1) / FS_WARPS);
+            shared_p1 = pick_state(S, (per_block + FS_WARPS - 1) / FS_WARPS);
     }
     auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
         chunk_fn fn = pick(S, rev);
@@ -654,7 +663,8 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
             if (!rev && in_band == 0 && shared_p1) {
                 // every band reads the same record: one read of each tile for all bands
                 const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
-                shared_p1<<<dim3(grid.y, C), FS_WARPS * 32, smem1, ctx->stream>>>(a);
+                a.nsplit = nsplit;
+                shared_p1<<<dim3(grid.y, C, nsplit), FS_WARPS * 32, smem1, ctx->stream>>>(a);
             } else {
                 fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
             }
