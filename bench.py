@@ -421,7 +421,11 @@ def main():
             "clocks": r["clocks"], "gpu_launches": int(r["launches"]), "e2e": r["e2e"],
             "stage_ms": r["stage"], "wall_ms_per_step": r["wall_ms"] / args.steps,
             "roofline": {"kernel": kern, "bound": "fp32" if use32 else "fp64", "achieved": tfl, "peak": peak,
-                         "unit": "TFLOP/s", "frac": (tfl / peak) if tfl else None, "traffic": None,
+                         "unit": "TFLOP/s", "frac": (tfl / peak) if tfl else None,
+                         # DRAM bytes of all cross-correlation kernels per step, ncu (profiles/r1_xcorr_dram_traffic_2h.csv
+                         # x 12): 0.4 TB/s over the stage, i.e. not the bound
+                         "traffic": 184.7e9 if (args.workload == "c3" and args.hours is None and r["world"] == 1
+                                                and args.method == "auto") else None,
                          "peak_source": ("FP32" if use32 else "FP64") + " FMA microbenchmark run in this process, 2 flop per "
                                         "FMA (MEASURED_PEAKS.json has no such entry; the path is neither HBM- nor tensor-"
                                         "bound).  FFT butterflies are mostly unfused adds, so 0.5 is the ceiling of this "
