@@ -113,6 +113,11 @@ int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag);
 int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain, double* max_screen_err,
                      int32_t reset);
 
+/* NBLS_OPT_SCREEN_AUDIT results: the largest |FP32 screen value - FP64 FFT value| over EVERY searched lag of the audited
+ * pair-windows (normalised correlation units; the candidate band assumes this stays below 1e-5) and the number of lags
+ * compared, since creation / the last reset.  Synchronises. */
+int nbls_xcorr_audit(nbls_ctx* ctx, double* max_err_all_lags, int64_t* n_lags, int32_t reset);
+
 /* Two-stage lag search of NBLS_XCORR_AUTO (all 2N-1 lags requested, FP32 screen): stage A searches |lag| <= k0 with a
  * shorter transform and proves for every pair-window - Cauchy-Schwarz over the partial energies of the two windows - that no
  * lag beyond k0 can reach the maximum found; pair-windows without a proof are redone over all lags, so the result is the
@@ -120,6 +125,8 @@ int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain,
  * bands to the single-stage search.  Returns the windows searched in two stages and those that held at least one redone
  * pair-window, since creation / the last reset. */
 int nbls_xcorr_two_stage_stats(nbls_ctx* ctx, int64_t* n_windows, int64_t* n_redone, int32_t reset);
+/* Pair-windows the second stage redid over all lags since creation / the last reset (the unit stage B works in). */
+int nbls_xcorr_two_stage_pairs(nbls_ctx* ctx, int64_t* n_redone_pairs, int32_t reset);
 
 /* ---- K3: per-window statistics and slowness solve ---------------------------------- */
 typedef struct nbls_solve_desc {
@@ -180,6 +187,12 @@ int nbls_run_device(nbls_ctx* ctx, const nbls_job* job, const double* x_dev, int
 int nbls_run_host(nbls_ctx* ctx, const nbls_job* job, const double* x_host, int32_t nchan,
                   int64_t npts, int64_t ldx_host, const nbls_outputs* out_host);
 
+/* Solve again on the integer lags and cmax the context kept from its last nbls_run_host call (same record, same window
+ * grid) with another solver description - e.g. the FAST-LTS pass of an OLS + LTS sweep over one record
+ * (the cross-correlation, > 90 % of a run, is shared; the reference would call ltsva twice, ltsva.py:45-54) - and
+ * copy the non-NULL estimate members of `out_host` back (lag and cmax members are ignored).  Synchronises. */
+int nbls_resolve_host(nbls_ctx* ctx, const nbls_solve_desc* sol, const nbls_outputs* out_host);
+
 /* ---- context, memory, diagnostics --------------------------------------------------- */
 int nbls_version(void);
 const char* nbls_last_error(void);
@@ -199,10 +212,38 @@ int nbls_host_unregister(void* ptr);
 int nbls_memcpy_h2d(nbls_ctx* ctx, void* dst_dev, const void* src_host, size_t bytes);
 int nbls_memcpy_d2h(nbls_ctx* ctx, void* dst_host, const void* src_dev, size_t bytes);
 
+/* ---- options: per context, set explicitly; libnbls reads nothing from the environment -------------------- */
+#define NBLS_OPT_PROFILE 0           /* 1: time every kernel group with CUDA events (nbls_profile); the context then
+                                        synchronises after each group, so whole-run times are not representative */
+#define NBLS_OPT_TWO_STAGE 1         /* 1 (default): two-stage lag search under NBLS_XCORR_AUTO; 0: single stage */
+#define NBLS_OPT_FILTER_SPLIT 2      /* blocks per (32 chunks, channel) tile of the shared forward phase 1; default 1 */
+#define NBLS_OPT_FILTER_SHARED_P1 3  /* 1 (default): forward phase 1 reads the raw record once for all bands */
+#define NBLS_OPT_FILTER_LANES 4      /* target number of time chunks in flight (auto chunk length); default 131072 */
+#define NBLS_OPT_LTS_FP64_RANK 5     /* 1: h-subsets by FP64 rank counting instead of FP16 keys (same subsets) */
+#define NBLS_OPT_SCREEN_AUDIT 6      /* 1: the FP32-screen path also runs the FP64 transform of every pair-window and
+                                        records the largest |FP32 - FP64| over ALL searched lags (nbls_xcorr_stats'
+                                        max_screen_err then covers every lag, not only the maximum); slow, for tests */
+#define NBLS_OPT_COUNT 16
+int nbls_set_option(nbls_ctx* ctx, int32_t key, int64_t value);
+int nbls_get_option(nbls_ctx* ctx, int32_t key, int64_t* value);
+
+/* Per-kernel-group profile, filled while NBLS_OPT_PROFILE is 1: device milliseconds (CUDA events on the context's
+ * stream around the group's launches), launches, and the ALGORITHMIC work the launches executed - flop for the
+ * cross-correlation and solve groups, bytes for the filter groups (DESIGN.md section 5 gives the formulas).
+ * Groups are numbered 0 .. nbls_kernel_group_count()-1; any output pointer may be NULL; reset != 0 clears the group. */
+int nbls_kernel_group_count(void);
+const char* nbls_kernel_group_name(int32_t group);
+int nbls_profile(nbls_ctx* ctx, int32_t group, double* ms, int64_t* launches, double* work, int32_t reset);
+
 /* Device time of the stages of the last nbls_run_* call, milliseconds, measured with CUDA
  * events on the context's stream: [0] H2D, [1] filter, [2] xcorr, [3] solve, [4] D2H,
  * [5] total.  Synchronises.  Returns the number of values written (<= n). */
 int nbls_last_timings(nbls_ctx* ctx, float* ms, int32_t n);
+/* Caller-placed time stamps on the context's stream (CUDA events; slots 0..7): nbls_mark records one, nbls_mark_elapsed
+ * waits for slot `b` and returns the device milliseconds between slots `a` and `b`.  For timing sequences of calls
+ * (e.g. a batch of arrays) on the stream the kernels actually run on. */
+int nbls_mark(nbls_ctx* ctx, int32_t slot);
+int nbls_mark_elapsed(nbls_ctx* ctx, int32_t a, int32_t b, float* ms);
 /* Kernel launches issued by this context since creation (for bench.py's gpu_launches). */
 int64_t nbls_launch_count(nbls_ctx* ctx);
 /* Register-resident DFMA throughput microbenchmark: returns FP64 TFLOP/s (2 flop per FMA)

@@ -21,6 +21,9 @@ c_int64_p = C.POINTER(C.c_int64)
 c_uint8_p = C.POINTER(C.c_uint8)
 
 XCORR_AUTO, XCORR_DIRECT, XCORR_FFT, XCORR_FFT32 = 0, 1, 2, 3
+# nbls_set_option keys (include/nbls.h)
+(OPT_PROFILE, OPT_TWO_STAGE, OPT_FILTER_SPLIT, OPT_FILTER_SHARED_P1, OPT_FILTER_LANES, OPT_LTS_FP64_RANK,
+ OPT_SCREEN_AUDIT) = range(7)
 
 
 class FilterDesc(C.Structure):
@@ -77,13 +80,23 @@ EXPORTS = {
     "nbls_xcorr_fft_length": (C.c_int, [C.c_int32, C.c_int32]),
     "nbls_xcorr_stats": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p, c_double_p, C.c_int32]),
     "nbls_xcorr_two_stage_stats": (C.c_int, [C.c_void_p, c_int64_p, c_int64_p, C.c_int32]),
+    "nbls_xcorr_audit": (C.c_int, [C.c_void_p, c_double_p, c_int64_p, C.c_int32]),
+    "nbls_xcorr_two_stage_pairs": (C.c_int, [C.c_void_p, c_int64_p, C.c_int32]),
+    "nbls_set_option": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64]),
+    "nbls_get_option": (C.c_int, [C.c_void_p, C.c_int32, c_int64_p]),
+    "nbls_kernel_group_count": (C.c_int, []),
+    "nbls_kernel_group_name": (C.c_char_p, [C.c_int32]),
+    "nbls_profile": (C.c_int, [C.c_void_p, C.c_int32, c_double_p, c_int64_p, c_double_p, C.c_int32]),
     "nbls_solve": (C.c_int, [C.c_void_p, C.POINTER(SolveDesc), C.c_int64, C.c_void_p, C.c_void_p,
                              C.POINTER(Outputs)]),
     "nbls_run_device": (C.c_int, [C.c_void_p, C.POINTER(Job), C.c_void_p, C.c_int32, C.c_int64, C.c_int64,
                                   C.POINTER(Outputs)]),
     "nbls_run_host": (C.c_int, [C.c_void_p, C.POINTER(Job), C.c_void_p, C.c_int32, C.c_int64, C.c_int64,
                                 C.POINTER(Outputs)]),
+    "nbls_resolve_host": (C.c_int, [C.c_void_p, C.POINTER(SolveDesc), C.POINTER(Outputs)]),
     "nbls_last_timings": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int32]),
+    "nbls_mark": (C.c_int, [C.c_void_p, C.c_int32]),
+    "nbls_mark_elapsed": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "nbls_launch_count": (C.c_int64, [C.c_void_p]),
     "nbls_measure_fp64_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
     "nbls_measure_fp32_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),

@@ -6,6 +6,8 @@
 #include <algorithm>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "common.cuh"
 
 namespace nbls {
@@ -39,6 +41,27 @@ int ensure(nbls_ctx* ctx, DevBuf& b, size_t bytes) {
     return NBLS_OK;
 }
 
+
+static const char* const kGroupNames[KG_COUNT] = {
+    "filter_fwd_phase1", "filter_fwd_phase3", "filter_bwd_phase1", "filter_bwd_phase3", "filter_carry",
+    "xf_spectra", "xf_pair", "xf_verify", "xf_verify_items", "xcorr_direct", "stats_ols", "lts"};
+
+KernelGroupScope::KernelGroupScope(nbls_ctx* ctx, int group, double work) : c(ctx), g(group) {
+    nvtxRangePushA(kGroupNames[group]);
+    c->prof_work[g] += work;
+    if (c->opt[NBLS_OPT_PROFILE]) cudaEventRecord(c->pev[0], c->stream);
+}
+KernelGroupScope::~KernelGroupScope() {
+    if (c->opt[NBLS_OPT_PROFILE]) {
+        float ms = 0.f;
+        if (cudaEventRecord(c->pev[1], c->stream) == cudaSuccess && cudaEventSynchronize(c->pev[1]) == cudaSuccess &&
+            cudaEventElapsedTime(&ms, c->pev[0], c->pev[1]) == cudaSuccess) {
+            c->prof_ms[g] += ms;
+            c->prof_n[g] += 1;
+        }
+    }
+    nvtxRangePop();
+}
 
 static int validate_windows(const nbls_window_desc* w, int C, int64_t ldy, int64_t* total) {
     NBLS_REQUIRE(w && w->win_len && w->win_hop && w->win_first && w->win_count, "nbls_xcorr: null window arrays");
@@ -254,6 +277,11 @@ int nbls_create(nbls_ctx** out, int32_t device) {
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     NBLS_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     for (int i = 0; i < EV_COUNT; ++i) NBLS_CUDA(cudaEventCreate(&ctx->ev[i]));
+    for (int i = 0; i < 2; ++i) NBLS_CUDA(cudaEventCreate(&ctx->pev[i]));
+    ctx->opt[NBLS_OPT_TWO_STAGE] = 1;
+    ctx->opt[NBLS_OPT_FILTER_SPLIT] = 1;
+    ctx->opt[NBLS_OPT_FILTER_SHARED_P1] = 1;
+    ctx->opt[NBLS_OPT_FILTER_LANES] = 131072;
     *out = ctx;
     return NBLS_OK;
 }
@@ -264,13 +292,17 @@ int nbls_destroy(nbls_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->coef, &ctx->state, &ctx->carry, &ctx->taper, &ctx->filt, &ctx->geom, &ctx->lts_tab,
                       &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch, &ctx->spec,
-                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat, &ctx->wfail};
+                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat, &ctx->wfail, &ctx->audit};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& kv : ctx->fft_tw)
         if (kv.second) cudaFree(kv.second);
     for (int i = 0; i < EV_COUNT; ++i)
         if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < 2; ++i)
+        if (ctx->pev[i]) cudaEventDestroy(ctx->pev[i]);
+    for (int i = 0; i < 8; ++i)
+        if (ctx->mark[i]) cudaEventDestroy(ctx->mark[i]);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return NBLS_OK;
@@ -285,6 +317,32 @@ int nbls_synchronize(nbls_ctx* ctx) {
 int nbls_set_workspace_limit(nbls_ctx* ctx, size_t bytes) {
     NBLS_REQUIRE(ctx, "nbls_set_workspace_limit: null context");
     ctx->ws_limit = bytes;
+    return NBLS_OK;
+}
+
+int nbls_set_option(nbls_ctx* ctx, int32_t key, int64_t value) {
+    NBLS_REQUIRE(ctx, "nbls_set_option: null context");
+    NBLS_REQUIRE(key >= 0 && key < NBLS_OPT_COUNT, "nbls_set_option: unknown option %d", key);
+    if (key == NBLS_OPT_FILTER_SPLIT) NBLS_REQUIRE(value >= 1 && value <= 64, "nbls_set_option: filter split %lld out of range", (long long)value);
+    if (key == NBLS_OPT_FILTER_LANES) NBLS_REQUIRE(value >= 32, "nbls_set_option: filter lanes %lld out of range", (long long)value);
+    ctx->opt[key] = value;
+    return NBLS_OK;
+}
+int nbls_get_option(nbls_ctx* ctx, int32_t key, int64_t* value) {
+    NBLS_REQUIRE(ctx && value, "nbls_get_option: null argument");
+    NBLS_REQUIRE(key >= 0 && key < NBLS_OPT_COUNT, "nbls_get_option: unknown option %d", key);
+    *value = ctx->opt[key];
+    return NBLS_OK;
+}
+int nbls_kernel_group_count(void) { return KG_COUNT; }
+const char* nbls_kernel_group_name(int32_t group) { return group >= 0 && group < KG_COUNT ? kGroupNames[group] : ""; }
+int nbls_profile(nbls_ctx* ctx, int32_t group, double* ms, int64_t* launches, double* work, int32_t reset) {
+    NBLS_REQUIRE(ctx, "nbls_profile: null context");
+    NBLS_REQUIRE(group >= 0 && group < KG_COUNT, "nbls_profile: group %d out of range", group);
+    if (ms) *ms = ctx->prof_ms[group];
+    if (launches) *launches = ctx->prof_n[group];
+    if (work) *work = ctx->prof_work[group];
+    if (reset) { ctx->prof_ms[group] = 0.0; ctx->prof_n[group] = 0; ctx->prof_work[group] = 0.0; }
     return NBLS_OK;
 }
 
@@ -369,7 +427,7 @@ int nbls_xcorr_fft_length(int32_t win_len, int32_t max_lag) { return xcorr_fft_l
 int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain, double* max_screen_err, int32_t reset) {
     NBLS_REQUIRE(ctx, "nbls_xcorr_stats: null context");
     NBLS_CUDA(cudaSetDevice(ctx->device));
-    unsigned long long h[4] = {0, 0, 0, 0};
+    unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (ctx->xstat.p) {
         NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
         NBLS_CUDA(cudaMemcpy(h, ctx->xstat.p, sizeof(h), cudaMemcpyDeviceToHost));
@@ -383,6 +441,24 @@ int nbls_xcorr_stats(nbls_ctx* ctx, int64_t* n_verified, int64_t* n_time_domain,
         memcpy(&f, &bits, sizeof(f));
         *max_screen_err = (double)f;
     }
+    if (ctx->xstat.p && (h[3] || h[4])) {
+        // audit counters are folded into the host copies and cleared on the device every time they are read
+        const unsigned int bits = (unsigned int)h[3];
+        float f;
+        memcpy(&f, &bits, sizeof(f));
+        ctx->audit_err = std::max(ctx->audit_err, (double)f);
+        ctx->audit_lags += (int64_t)h[4];
+        NBLS_CUDA(cudaMemset((char*)ctx->xstat.p + 3 * sizeof(unsigned long long), 0, 2 * sizeof(unsigned long long)));
+    }
+    return NBLS_OK;
+}
+
+int nbls_xcorr_audit(nbls_ctx* ctx, double* max_err_all_lags, int64_t* n_lags, int32_t reset) {
+    NBLS_REQUIRE(ctx, "nbls_xcorr_audit: null context");
+    NBLS_CHECK(nbls_xcorr_stats(ctx, nullptr, nullptr, nullptr, 0));     // folds the device counters into the host copies
+    if (max_err_all_lags) *max_err_all_lags = ctx->audit_err;
+    if (n_lags) *n_lags = ctx->audit_lags;
+    if (reset) { ctx->audit_err = 0.0; ctx->audit_lags = 0; }
     return NBLS_OK;
 }
 
@@ -391,6 +467,13 @@ int nbls_xcorr_two_stage_stats(nbls_ctx* ctx, int64_t* n_windows, int64_t* n_red
     if (n_windows) *n_windows = ctx->ts_windows;
     if (n_redone) *n_redone = ctx->ts_redone;
     if (reset) { ctx->ts_windows = 0; ctx->ts_redone = 0; ctx->ts_skip = 0; }
+    return NBLS_OK;
+}
+
+int nbls_xcorr_two_stage_pairs(nbls_ctx* ctx, int64_t* n_redone_pairs, int32_t reset) {
+    NBLS_REQUIRE(ctx, "nbls_xcorr_two_stage_pairs: null context");
+    if (n_redone_pairs) *n_redone_pairs = ctx->ts_redone_pairs;
+    if (reset) ctx->ts_redone_pairs = 0;
     return NBLS_OK;
 }
 
@@ -463,6 +546,42 @@ int nbls_run_host(nbls_ctx* ctx, const nbls_job* job, const double* x_host, int3
     NBLS_CHECK(record(ctx, EV_D2H));
     NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->ev_valid = true;
+    ctx->last_E = E;
+    ctx->last_P = P;
+    return NBLS_OK;
+}
+
+int nbls_resolve_host(nbls_ctx* ctx, const nbls_solve_desc* sol, const nbls_outputs* oh) {
+    NBLS_REQUIRE(ctx && sol && oh, "nbls_resolve_host: null argument");
+    NBLS_REQUIRE(ctx->last_E >= 0, "nbls_resolve_host: no nbls_run_host call to re-solve");
+    NBLS_REQUIRE(sol->npairs == ctx->last_P, "nbls_resolve_host: %d pairs, the retained lags have %d", sol->npairs,
+                 (int)ctx->last_P);
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    const int64_t E = ctx->last_E, En = std::max<int64_t>(E, 1);
+    const int P = sol->npairs;
+    const bool lts = sol->alpha != 1.0;
+    if (lts) NBLS_CHECK(ensure(ctx, ctx->wbuf, (size_t)En * P));
+    double* r = (double*)ctx->res.p;
+    nbls_outputs od;
+    memset(&od, 0, sizeof(od));
+    od.mdccm = r; od.mad = r + En; od.vel = r + 2 * En; od.baz = r + 3 * En; od.sigma_tau = r + 4 * En;
+    od.slowness = r + 5 * En;
+    od.weights = lts ? (uint8_t*)ctx->wbuf.p : nullptr;
+    if (E > 0) {
+        NBLS_CHECK(solve_impl(ctx, sol, E, (const int32_t*)ctx->lagbuf.p, (const double*)ctx->cmaxbuf.p, &od));
+        auto back = [&](void* dst, const void* src, size_t bytes) -> int {
+            if (dst) NBLS_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+            return NBLS_OK;
+        };
+        NBLS_CHECK(back(oh->mdccm, od.mdccm, E * sizeof(double)));
+        NBLS_CHECK(back(oh->mad, od.mad, E * sizeof(double)));
+        NBLS_CHECK(back(oh->vel, od.vel, E * sizeof(double)));
+        NBLS_CHECK(back(oh->baz, od.baz, E * sizeof(double)));
+        NBLS_CHECK(back(oh->sigma_tau, od.sigma_tau, E * sizeof(double)));
+        NBLS_CHECK(back(oh->slowness, od.slowness, 2 * E * sizeof(double)));
+        if (lts) NBLS_CHECK(back(oh->weights, od.weights, (size_t)E * P));
+    }
+    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
     return NBLS_OK;
 }
 
@@ -485,6 +604,21 @@ int nbls_last_timings(nbls_ctx* ctx, float* ms, int32_t n) {
     const int m = std::min<int>(n, 6);
     for (int i = 0; i < m; ++i) ms[i] = v[i];
     return m;
+}
+
+int nbls_mark(nbls_ctx* ctx, int32_t slot) {
+    NBLS_REQUIRE(ctx && slot >= 0 && slot < 8, "nbls_mark: bad argument");
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->mark[slot]) NBLS_CUDA(cudaEventCreate(&ctx->mark[slot]));
+    NBLS_CUDA(cudaEventRecord(ctx->mark[slot], ctx->stream));
+    return NBLS_OK;
+}
+int nbls_mark_elapsed(nbls_ctx* ctx, int32_t a, int32_t b, float* ms) {
+    NBLS_REQUIRE(ctx && ms && a >= 0 && a < 8 && b >= 0 && b < 8 && ctx->mark[a] && ctx->mark[b],
+                 "nbls_mark_elapsed: bad argument or unrecorded slot");
+    NBLS_CUDA(cudaEventSynchronize(ctx->mark[b]));
+    NBLS_CUDA(cudaEventElapsedTime(ms, ctx->mark[a], ctx->mark[b]));
+    return NBLS_OK;
 }
 
 int64_t nbls_launch_count(nbls_ctx* ctx) { return ctx ? ctx->launches : -1; }

@@ -47,6 +47,23 @@ struct DevBuf {
 
 enum { EV_START = 0, EV_H2D, EV_FILTER, EV_XCORR, EV_SOLVE, EV_D2H, EV_COUNT };
 
+// kernel groups of the per-group profile (nbls_profile) — keep nbls_kernel_group_name() in api.cu in step
+enum {
+    KG_FILTER_P1F = 0,   // forward phase 1 (chunk end states)
+    KG_FILTER_P3F,       // forward phase 3 (output)
+    KG_FILTER_P1B,       // backward phase 1
+    KG_FILTER_P3B,       // backward phase 3 (output + taper)
+    KG_FILTER_CARRY,     // both carry kernels
+    KG_SPECTRA,          // xf_spectra_kernel
+    KG_PAIR,             // xf_pair_kernel
+    KG_VERIFY,           // xf_verify_kernel
+    KG_VERIFY_ITEMS,     // xf_verify_items_kernel (stage B)
+    KG_DIRECT,           // xcorr_direct_kernel (whole bands or the near-tie list)
+    KG_STATS_OLS,        // stats_ols_kernel
+    KG_LTS,              // lts_kernel
+    KG_COUNT
+};
+
 }  // namespace nbls
 
 namespace nbls {
@@ -73,6 +90,7 @@ struct nbls_ctx {
     nbls::DevBuf coef, state, carry, taper, filt, geom, lts_tab, xin, res, lagbuf, cmaxbuf, wbuf, scratch;
     nbls::DevBuf spec, energy, flags;       // FFT cross-correlation workspace
     nbls::DevBuf cand, sval, xstat;         // FP32 screen: candidate lags, screen maxima; xcorr statistics
+    nbls::DevBuf audit;                     // NBLS_OPT_SCREEN_AUDIT workspace
     nbls::DevBuf wfail;                     // two-stage lag search: failing pair-window items and the window list of stage B
     int ts_skip = 0;                        // bands left to the single-stage search after a band that mostly failed
     int64_t ts_windows = 0, ts_redone = 0;  // two-stage statistics: windows searched / redone over all lags
@@ -80,7 +98,32 @@ struct nbls_ctx {
     cudaEvent_t ev[nbls::EV_COUNT] = {};
     bool ev_valid = false;
     float stage_ms[6] = {};
+    // options (nbls_set_option) — per context, never read from the environment
+    int64_t opt[NBLS_OPT_COUNT] = {};
+    // per-kernel-group profile (NBLS_OPT_PROFILE): device ms, launches, executed algorithmic work (flop, or bytes for the
+    // filter groups) since the last reset
+    cudaEvent_t pev[2] = {};
+    cudaEvent_t mark[8] = {};               // nbls_mark slots, created on first use
+    double prof_ms[nbls::KG_COUNT] = {};
+    int64_t prof_n[nbls::KG_COUNT] = {};
+    double prof_work[nbls::KG_COUNT] = {};
+    double audit_err = 0.0;                 // NBLS_OPT_SCREEN_AUDIT: largest |FP32 - FP64| over every searched lag
+    int64_t audit_lags = 0;
+    int64_t last_E = -1, last_P = 0;        // rows / pairs of the lags kept by the last nbls_run_host (nbls_resolve_host)
+    int64_t ts_redone_pairs = 0;            // two-stage: pair-windows redone over all lags
 };
+
+namespace nbls {
+// Brackets the launches of one kernel group: an NVTX range always (visible in nsys / ncu --nvtx), and with
+// NBLS_OPT_PROFILE a CUDA-event pair on the context's stream whose elapsed time is added to the group (this
+// synchronises after every group, so a profiled run is slower as a whole; the per-group times are what it is for).
+struct KernelGroupScope {
+    nbls_ctx* c;
+    int g;
+    KernelGroupScope(nbls_ctx* ctx, int group, double work);
+    ~KernelGroupScope();
+};
+}  // namespace nbls
 
 namespace nbls {
 

@@ -565,7 +565,7 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     // chunking
     int64_t L = d->chunk_len;
     if (L <= 0) {
-        const double lanes = getenv("NBLS_FILTER_LANES") ? atof(getenv("NBLS_FILTER_LANES")) : 131072.0;
+        const double lanes = (double)ctx->opt[NBLS_OPT_FILTER_LANES];
         L = round_up((int64_t)((double)T * B * C / lanes), FT_TILE);
         L = std::max<int64_t>(256, std::min<int64_t>(65536, L));
     }
@@ -646,10 +646,9 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     {
         bool mono = true;
         for (int b = 1; b < B; ++b) mono = mono && hproc[b] <= hproc[b - 1];
-        if (getenv("NBLS_FILTER_SPLIT")) nsplit = std::max(1, atoi(getenv("NBLS_FILTER_SPLIT")));
-        else nsplit = 1;
+        nsplit = (int)std::max<int64_t>(1, ctx->opt[NBLS_OPT_FILTER_SPLIT]);
         const int per_block = (B + nsplit - 1) / nsplit;
-        if (mono && nchunks > 1 && !getenv("NBLS_FILTER_NO_SHARED_P1"))
+        if (mono && nchunks > 1 && ctx->opt[NBLS_OPT_FILTER_SHARED_P1])
             shared_p1 = pick_state(S, (per_block + FS_WARPS - 1) / FS_WARPS);
     }
     auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
@@ -660,16 +659,22 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         a.coef = dcoef; a.B = B; a.C = C; a.T = T; a.L = (int)L; a.nchunks = nchunks;
         if (nchunks > 1) {
             a.out = nullptr; a.proc_tiles = dproc; a.state_in = nullptr; a.state_out = dstate;
-            if (!rev && in_band == 0 && shared_p1) {
-                // every band reads the same record: one read of each tile for all bands
-                const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
-                a.nsplit = nsplit;
-                shared_p1<<<dim3(grid.y, C, nsplit), FS_WARPS * 32, smem1, ctx->stream>>>(a);
-            } else {
-                fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+            {
+                KernelGroupScope ks(ctx, rev ? KG_FILTER_P1B : KG_FILTER_P1F, 0.0);   // state passes: no algorithmic bytes
+                if (!rev && in_band == 0 && shared_p1) {
+                    // every band reads the same record: one read of each tile for all bands
+                    const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
+                    a.nsplit = nsplit;
+                    shared_p1<<<dim3(grid.y, C, nsplit), FS_WARPS * 32, smem1, ctx->stream>>>(a);
+                } else {
+                    fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+                }
             }
             NBLS_CUDA(cudaGetLastError());
-            pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, rev ? 1 : 0);
+            {
+                KernelGroupScope ks(ctx, KG_FILTER_CARRY, 0.0);
+                pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, rev ? 1 : 0);
+            }
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 2;
         }
@@ -679,7 +684,12 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
             a.taper_up = dup; a.taper_down = ddown; a.taper_len = d->taper_len; a.g0 = d->global_t0;
             a.G = d->global_npts > 0 ? d->global_npts : T;
         }
-        fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+        {
+            // algorithmic bytes: the raw record is read once for all bands (in_band == 0), a filtered band once; one write
+            const double rd = in_band == 0 ? 8.0 * C * (double)T : 8.0 * B * C * (double)T;
+            KernelGroupScope ks(ctx, rev ? KG_FILTER_P3B : KG_FILTER_P3F, rd + 8.0 * B * C * (double)T);
+            fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 1;
         return NBLS_OK;

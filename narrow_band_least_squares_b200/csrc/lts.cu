@@ -427,10 +427,13 @@ int lts_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_
     static const lts_fn table[11] = {lts_kernel<0>, lts_kernel<1>, lts_kernel<2>, lts_kernel<3>, lts_kernel<4>, lts_kernel<5>,
                                      lts_kernel<6>, lts_kernel<7>, lts_kernel<8>, lts_kernel<9>, lts_kernel<10>};
     const int ni = (P + 31) / 32;
-    const lts_fn fn = table[(ni <= 10 && !getenv("NBLS_LTS_FP64_RANK")) ? ni : 0];
+    const lts_fn fn = table[(ni <= 10 && !ctx->opt[NBLS_OPT_LTS_FP64_RANK]) ? ni : 0];
     NBLS_CUDA(allow_max_dynamic_smem(fn, ctx->smem_optin));
     const int grid = (int)std::min<int64_t>(nwin, (int64_t)ctx->sm_count * 32);
-    fn<<<grid, LTS_WARPS * 32, smem, ctx->stream>>>(a);
+    {
+        KernelGroupScope ks(ctx, KG_LTS, 0.0);
+        fn<<<grid, LTS_WARPS * 32, smem, ctx->stream>>>(a);
+    }
     NBLS_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return NBLS_OK;

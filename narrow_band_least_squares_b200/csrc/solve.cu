@@ -108,7 +108,10 @@ int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int3
     NBLS_CUDA(allow_max_dynamic_smem(stats_ols_kernel, ctx->smem_optin));
     const int64_t want = (nwin + OLS_WARPS - 1) / OLS_WARPS;
     const int grid = (int)std::min<int64_t>(want, (int64_t)ctx->sm_count * 16);
-    stats_ols_kernel<<<grid, OLS_WARPS * 32, smem, ctx->stream>>>(a);
+    {
+        KernelGroupScope ks(ctx, KG_STATS_OLS, (double)nwin * 10.0 * P);
+        stats_ols_kernel<<<grid, OLS_WARPS * 32, smem, ctx->stream>>>(a);
+    }
     NBLS_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return NBLS_OK;

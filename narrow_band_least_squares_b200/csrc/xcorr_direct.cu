@@ -225,7 +225,11 @@ int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, in
     NBLS_CUDA(allow_max_dynamic_smem(xcorr_direct_kernel, ctx->smem_optin));
     const int64_t nblocks = list ? std::min<int64_t>((int64_t)W * P, std::max(1, grid_cap)) : (int64_t)W * P;
     NBLS_REQUIRE(nblocks < (1LL << 31), "nbls_xcorr: too many (window, pair) items in one band: %lld", (long long)nblocks);
-    xcorr_direct_kernel<<<(unsigned)nblocks, nwarps * 32, smem, ctx->stream>>>(a);
+    {
+        // executed work is known on the host only for whole bands (M^2 multiply-adds per pair-window); list mode adds none
+        KernelGroupScope ks(ctx, KG_DIRECT, list ? 0.0 : (double)W * P * 2.0 * (double)a.M * (double)a.M);
+        xcorr_direct_kernel<<<(unsigned)nblocks, nwarps * 32, smem, ctx->stream>>>(a);
+    }
     NBLS_CUDA(cudaGetLastError());
     ctx->launches += 1;
     return NBLS_OK;

@@ -84,6 +84,10 @@ struct XfArgs {
     const int* wlist;     // window-list mode: band-level window index of launch slot s; nullptr = w0 + s
     const int* items;     // item mode (pair kernel, xf_verify_items_kernel): sorted batch items wl*P+p, two per pair CTA
     int n_items;
+    // audit (NBLS_OPT_SCREEN_AUDIT): the pair kernel also stores the whole circular correlation function of every
+    // pair-window with wl < dump_wn - [dump_wn * P][L] reals of the transform's precision, unnormalised (value * L)
+    void* dump;
+    int dump_wn;
 };
 
 __device__ __forceinline__ int win_index(const XfArgs& g, int s) { return g.wlist ? g.wlist[s] : g.w0 + s; }
@@ -472,6 +476,14 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         Dft<S::R3>::run(z);
         const int n1 = u / S::R2, n2 = u - n1 * S::R2;
         const int nb = n1 + R1 * n2;
+        if (g.dump && act && !g.items) {
+            F* d = static_cast<F*>(g.dump);
+#pragma unroll
+            for (int n3 = 0; n3 < S::R3; ++n3) {
+                if (wl0 < g.dump_wn) d[((int64_t)wl0 * g.P + p0) * L + nb + STEP * n3] = z[n3].x;
+                if (has1 && wl1 < g.dump_wn) d[((int64_t)wl1 * g.P + p1) * L + nb + STEP * n3] = z[n3].y;
+            }
+        }
         // circular index n = nb + R1 R2 n3 stands for lag n (n <= lag_max) or n - L (n >= L - lag_max): the wanted
         // n3 are [0, n3a] and [n3b, R3)
         const int n3a = !act ? -1 : (lag_max >= nb ? (lag_max - nb) / STEP : -1);
@@ -533,8 +545,18 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             } else {
                 give = true;
             }
+            // the candidates arrive in the order the atomics ran in; sorted by lag, slot s always holds the same lag, so the
+            // exact sums (slot 0: slice tree, slots 1..: one warp-strided pass) do not depend on the arrival order
+            int cl[XF_KC];
 #pragma unroll
-            for (int s_ = 0; s_ < XF_KC; ++s_) cd[s_] = (give && s_ < cnt) ? scl[tid][s_] : INT_MIN;
+            for (int s_ = 0; s_ < XF_KC; ++s_) cl[s_] = (give && s_ < cnt) ? scl[tid][s_] : INT_MAX;
+#pragma unroll
+            for (int i_ = 1; i_ < XF_KC; ++i_)
+#pragma unroll
+                for (int j_ = XF_KC - 1; j_ >= i_; --j_)
+                    if (cl[j_] < cl[j_ - 1]) { const int t_ = cl[j_]; cl[j_] = cl[j_ - 1]; cl[j_ - 1] = t_; }
+#pragma unroll
+            for (int s_ = 0; s_ < XF_KC; ++s_) cd[s_] = cl[s_] == INT_MAX ? INT_MIN : cl[s_];
             g.sval[loc] = (tid == 0 ? mr : mi) / (float)L;
         }
     } else {
@@ -557,6 +579,14 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         Dft<S::R3>::run(z);
         const int n1 = u / S::R2, n2 = u - n1 * S::R2;
         const int nb = n1 + R1 * n2;
+        if (g.dump && !g.items) {
+            F* d = static_cast<F*>(g.dump);
+#pragma unroll
+            for (int n3 = 0; n3 < S::R3; ++n3) {
+                if (wl0 < g.dump_wn) d[((int64_t)wl0 * g.P + p0) * L + nb + STEP * n3] = z[n3].x;
+                if (has1 && wl1 < g.dump_wn) d[((int64_t)wl1 * g.P + p1) * L + nb + STEP * n3] = z[n3].y;
+            }
+        }
         // circular index n = nb + R1 R2 n3 stands for lag n (n <= lag_max) or n - L (n >= L - lag_max): the wanted
         // n3 are [0, n3a] and [n3b, R3); the chains record n3, the lag is rebuilt afterwards
         const int n3a = lag_max >= nb ? (lag_max - nb) / STEP : -1;
@@ -921,6 +951,38 @@ __global__ void __launch_bounds__(XV_SL * 32) xf_verify_items_kernel(XfArgs g) {
     }
 }
 
+// ---- audit (NBLS_OPT_SCREEN_AUDIT) ------------------------------------------------------------
+// Largest |FP32 screen value - FP64 FFT value| over EVERY searched lag of the dumped pair-windows, in normalised
+// correlation units, into stat[3] (float bits); stat[4] counts the lags compared.  One CTA per pair-window.
+__global__ void __launch_bounds__(256) xf_audit_kernel(const float* d32, const double* d64, int L, int lag_max,
+                                                       unsigned long long* stat) {
+    __shared__ float wmax[8];
+    const float* a = d32 + (int64_t)blockIdx.x * L;
+    const double* b = d64 + (int64_t)blockIdx.x * L;
+    float e = 0.f;
+    unsigned int n_ok = 0;
+    for (int n = threadIdx.x; n < L; n += 256) {
+        if (n <= lag_max || n >= L - lag_max) {
+            const double d = fabs((double)a[n] - b[n]) / (double)L;
+            if (d == d) { e = fmaxf(e, (float)d); ++n_ok; }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        e = fmaxf(e, __shfl_xor_sync(0xffffffffu, e, o));
+        n_ok += __shfl_xor_sync(0xffffffffu, n_ok, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        wmax[threadIdx.x >> 5] = e;
+        atomicAdd(stat + 4, (unsigned long long)n_ok);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int i = 1; i < 8; ++i) e = fmaxf(e, wmax[i]);
+        atomicMax(stat + 3, (unsigned long long)__float_as_uint(e));
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------
 typedef void (*xf_kernel)(XfArgs);
 struct XfPlan {
@@ -1046,7 +1108,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     const int lag_full = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
     // two-stage search: only for the full-lag request of the FP32 screen, and not while recent bands kept failing
     const XfPlan* pa = nullptr;
-    if (fp32 && two_stage && lag_full == N - 1 && !getenv("NBLS_NO_TWO_STAGE")) {
+    if (fp32 && two_stage && lag_full == N - 1 && ctx->opt[NBLS_OPT_TWO_STAGE]) {
         if (ctx->ts_skip > 0) --ctx->ts_skip;
         else pa = pick_stage_a(N, pl);
     }
@@ -1116,19 +1178,74 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
                                  ctx->sm_count * 2);
     };
     // one pass of spectra -> pair -> (verify) -> time-domain list over the windows described by `a`
+    // executed algorithmic flop of one complex transform of q->L points: 5 L log2 L; the pair kernel adds 16 L (two
+    // cross-spectra, packing, two screening compares per point); one exact candidate costs 2 N FP64 flop
+    auto fft_flop = [](const XfPlan* q) { return 5.0 * q->L * log2((double)q->L); };
+    // audit: the first `wa` windows of the pass also go through the FP64 transform of the same length and every
+    // searched lag is compared (xf_audit_kernel)
+    const bool audit = fp32 && ctx->opt[NBLS_OPT_SCREEN_AUDIT] != 0;
+    auto audit_pass = [&](const XfPlan* q, int wa) -> int {
+        const XfPlan* q64 = nullptr;
+        for (const XfPlan& p64 : plans(false))
+            if (p64.L == q->L) q64 = &p64;
+        if (!q64 || q64->smem > ctx->smem_optin) return NBLS_OK;
+        const void* tw64 = nullptr;
+        NBLS_CHECK(twiddles<double2>(ctx, q->L, &tw64));
+        const size_t n_it = (size_t)wa * P, SPq = (size_t)q->L / 2 + 1;
+        const size_t o_d64 = round_up(n_it * q->L * sizeof(float), 256);
+        const size_t o_spec = o_d64 + round_up(n_it * q->L * sizeof(double), 256);
+        const size_t o_int = o_spec + round_up((size_t)wa * C * SPq * sizeof(double2), 256);
+        char* base = (char*)ctx->audit.p;
+        XfArgs b = a;
+        b.first = a.first + (int64_t)a.w0 * a.hop; b.w0 = 0; b.wn = wa; b.k0 = -1; b.wlist = nullptr; b.items = nullptr;
+        b.tw = tw64; b.spec = base + o_spec;
+        b.lag = (int32_t*)(base + o_int); b.cmax = nullptr;
+        b.flag_count = b.lag + n_it; b.flag_list = b.flag_count + 4;
+        b.stat = (unsigned long long*)(base + o_int + round_up((2 * n_it + 8) * sizeof(int), 256));
+        b.dump = base + o_d64; b.dump_wn = wa;
+        NBLS_CUDA(cudaMemsetAsync(b.flag_count, 0, sizeof(int), ctx->stream));
+        NBLS_CUDA(cudaFuncSetAttribute(q64->spectra, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q64->smem));
+        NBLS_CUDA(cudaFuncSetAttribute(q64->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q64->smem));
+        q64->spectra<<<(unsigned)(wa * ncp), q64->threads, q64->smem, ctx->stream>>>(b);
+        NBLS_CUDA(cudaGetLastError());
+        q64->pair<<<(unsigned)(wa * npp), q64->threads, q64->smem, ctx->stream>>>(b);
+        NBLS_CUDA(cudaGetLastError());
+        xf_audit_kernel<<<(unsigned)n_it, 256, 0, ctx->stream>>>((const float*)base, (const double*)(base + o_d64), q->L,
+                                                               a.lag_max, a.stat);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 3;
+        return NBLS_OK;
+    };
     auto pass = [&](const XfPlan* q) -> int {
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
-        q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
+        int wa = 0;
+        a.dump = nullptr; a.dump_wn = 0;
+        if (audit) {
+            const size_t per_w = (size_t)P * q->L * 12 + (size_t)C * (q->L / 2 + 1) * 16 + (size_t)P * 8 + 1024;
+            wa = (int)std::min<size_t>((size_t)a.wn, std::max<size_t>(1, ((size_t)1 << 30) / per_w));
+            NBLS_CHECK(ensure(ctx, ctx->audit, (size_t)wa * per_w + 8192));
+            a.dump = ctx->audit.p; a.dump_wn = wa;
+        }
+        {
+            KernelGroupScope ks(ctx, KG_SPECTRA, (double)a.wn * ncp * fft_flop(q));
+            q->spectra<<<(unsigned)(a.wn * ncp), q->threads, q->smem, ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
-        q->pair<<<(unsigned)(a.wn * npp), q->threads, q->smem, ctx->stream>>>(a);
+        {
+            KernelGroupScope ks(ctx, KG_PAIR, (double)a.wn * npp * (fft_flop(q) + 16.0 * q->L));
+            q->pair<<<(unsigned)(a.wn * npp), q->threads, q->smem, ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 2;
         if (fp32) {
             const int nib = (C - 1 + ib - 1) / ib;
+            KernelGroupScope ks(ctx, KG_VERIFY, (double)a.wn * P * 2.0 * N);
             verify<<<(unsigned)(a.wn * nib), vnw * 32, vsmem, ctx->stream>>>(a);
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 1;
         }
+        if (wa > 0) NBLS_CHECK(audit_pass(q, wa));
+        a.dump = nullptr; a.dump_wn = 0;
         return settle();
     };
     int64_t n_redo = 0, n_redo_pairs = 0;
@@ -1172,12 +1289,21 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         a.SP = SP; a.tw = tw;
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
         a.wn = (int)hwin.size(); a.wlist = dwlist;
-        pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);
+        {
+            KernelGroupScope ks(ctx, KG_SPECTRA, (double)a.wn * ncp * fft_flop(pl));
+            pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
         a.wlist = nullptr; a.items = a.pf_list; a.n_items = nfail;
-        pl->pair<<<(unsigned)((nfail + 1) / 2), pl->threads, pl->smem, ctx->stream>>>(a);
+        {
+            KernelGroupScope ks(ctx, KG_PAIR, (double)((nfail + 1) / 2) * (fft_flop(pl) + 16.0 * pl->L));
+            pl->pair<<<(unsigned)((nfail + 1) / 2), pl->threads, pl->smem, ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
-        xf_verify_items_kernel<<<(unsigned)nfail, XV_SL * 32, (size_t)N * sizeof(double), ctx->stream>>>(a);
+        {
+            KernelGroupScope ks(ctx, KG_VERIFY_ITEMS, (double)nfail * 2.0 * N);
+            xf_verify_items_kernel<<<(unsigned)nfail, XV_SL * 32, (size_t)N * sizeof(double), ctx->stream>>>(a);
+        }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 3;
         NBLS_CHECK(settle());
@@ -1185,6 +1311,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     if (pa) {
         ctx->ts_windows += W;
         ctx->ts_redone += n_redo;
+        ctx->ts_redone_pairs += n_redo_pairs;
         // a band where most pair-windows had to be redone: leave the next three bands to the single-stage search
         if (n_redo_pairs * 2 > (int64_t)W * P) ctx->ts_skip = 3;
     }

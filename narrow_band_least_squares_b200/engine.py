@@ -93,6 +93,17 @@ class Plan:
     def band_rows(self, b):
         return slice(int(self.offsets[b]), int(self.offsets[b + 1]))
 
+    def with_alpha(self, alpha):
+        """The same job with another solver (OLS <-> FAST-LTS): same filter, window grid and co-array."""
+        import copy
+        p = copy.copy(self)
+        p.alpha = float(alpha)
+        job = _capi.Job()
+        C.memmove(C.byref(job), C.byref(self.job), C.sizeof(_capi.Job))
+        p.job = job
+        p._fill_solve(job.solve)
+        return p
+
 
 class Results:
     """Host arrays of one run, window-major over all bands (row e = offsets[b] + w)."""
@@ -188,6 +199,14 @@ class Engine:
                                      data.shape[1], C.byref(res.struct)))
         return res
 
+    def resolve(self, plan: Plan, results: Results | None = None) -> Results:
+        """Solve again on the lags this context kept from its last ``run`` with ``plan``'s solver description
+        (nbls_resolve_host) — the second leg of an OLS + LTS sweep.  ``plan`` must describe the same record and window
+        grid as the run (use ``Plan.with_alpha``)."""
+        res = results if results is not None else Results(plan, pinned=False, want_cmax=False)
+        check(self.lib.nbls_resolve_host(self.ctx, C.byref(plan.job.solve), C.byref(res.struct)))
+        return res
+
     def run_resident(self, plan: Plan, x_dev: DeviceArray, ldx, out_struct):
         """Device buffers in and out (nbls_run_device); asynchronous — call synchronize()."""
         check(self.lib.nbls_run_device(self.ctx, C.byref(plan.job), x_dev.ptr, plan.nchan, plan.npts, int(ldx),
@@ -217,6 +236,20 @@ class Engine:
             raise NBLSError(self.lib.nbls_last_error().decode())
         return dict(zip(("h2d", "filter", "xcorr", "solve", "d2h", "total"), (float(v) for v in buf)))
 
+    def mark(self, slot):
+        """Time stamp on the context's stream (nbls_mark)."""
+        check(self.lib.nbls_mark(self.ctx, int(slot)))
+
+    def elapsed(self, a, b):
+        """Device ms between two marks; waits for the second."""
+        v = C.c_float()
+        check(self.lib.nbls_mark_elapsed(self.ctx, int(a), int(b), C.byref(v)))
+        return float(v.value)
+
+    def solve_resident(self, plan: Plan, nwin, lag_ptr, cmax_ptr, out_struct):
+        """nbls_solve on device-resident lags / cmax with ``plan``'s solver description; asynchronous."""
+        check(self.lib.nbls_solve(self.ctx, C.byref(plan.job.solve), int(nwin), lag_ptr, cmax_ptr, C.byref(out_struct)))
+
     def launch_count(self):
         return int(self.lib.nbls_launch_count(self.ctx))
 
@@ -237,8 +270,34 @@ class Engine:
         check(self.lib.nbls_xcorr_stats(self.ctx, C.byref(nv), C.byref(nt), C.byref(err), int(bool(reset))))
         nw, nr = C.c_int64(), C.c_int64()
         check(self.lib.nbls_xcorr_two_stage_stats(self.ctx, C.byref(nw), C.byref(nr), int(bool(reset))))
+        npr = C.c_int64()
+        check(self.lib.nbls_xcorr_two_stage_pairs(self.ctx, C.byref(npr), int(bool(reset))))
         return dict(verified=nv.value, time_domain=nt.value, max_screen_err=err.value, two_stage_windows=nw.value,
-                    two_stage_redone=nr.value)
+                    two_stage_redone=nr.value, two_stage_redone_pairs=npr.value)
+
+    def xcorr_audit(self, reset=False):
+        """(largest |FP32 screen - FP64 FFT| over every searched lag, lags compared) while OPT_SCREEN_AUDIT was on."""
+        err, n = C.c_double(), C.c_int64()
+        check(self.lib.nbls_xcorr_audit(self.ctx, C.byref(err), C.byref(n), int(bool(reset))))
+        return err.value, n.value
+
+    def set_option(self, key, value):
+        """Per-context switch (nbls_set_option; keys are _capi.OPT_*)."""
+        check(self.lib.nbls_set_option(self.ctx, int(key), int(value)))
+
+    def get_option(self, key):
+        v = C.c_int64()
+        check(self.lib.nbls_get_option(self.ctx, int(key), C.byref(v)))
+        return v.value
+
+    def profile(self, reset=False):
+        """Per-kernel-group device ms / launches / executed algorithmic work gathered while OPT_PROFILE was on."""
+        out = {}
+        for g in range(self.lib.nbls_kernel_group_count()):
+            ms, n, wk = C.c_double(), C.c_int64(), C.c_double()
+            check(self.lib.nbls_profile(self.ctx, g, C.byref(ms), C.byref(n), C.byref(wk), int(bool(reset))))
+            out[self.lib.nbls_kernel_group_name(g).decode()] = dict(ms=ms.value, launches=n.value, work=wk.value)
+        return out
 
     # ---- stage level ------------------------------------------------------------------------
     def filter_bands(self, data, fs, sos_list, zerophase=True, taper=0.01, chunk_len=0, exact_scan=False,

@@ -103,8 +103,8 @@ def taper_ramps(npts, max_percentage=0.01):
 
 
 def make_float(input_list):
-    """helpers.py:145-158."""
-    return [float(v) for v in input_list]
+    """helpers.py:145-158: the values as a float ndarray."""
+    return np.array([float(v) for v in input_list])
 
 
 def filter_data(st, FILTER_TYPE, FMIN, FMAX, FILTER_ORDER, FILTER_RIPPLE):

@@ -53,15 +53,9 @@ def build_plan(nchan, npts, Fs, rij, WINLEN_list, WINOVER, ALPHA, NBANDS, freqli
                 max_lag=max_lag, method=method, **plan_kw)
 
 
-def narrow_band_least_squares(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_list, NBANDS, w, h, freqlist,
-                              FREQ_BAND_TYPE, freq_resp_list, FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE, *,
-                              rij=None, engine=None, max_lag=-1, method=_capi.XCORR_AUTO, return_details=False):
-    """Narrow-band least-squares array processing of ``st`` in ``NBANDS`` frequency bands.
-
-    Returns ``(vel_array, baz_array, mdccm_array, t_array, stdict_all, sig_tau_array,
-    num_compute_list, w_array, h_array)`` exactly like the reference (arrays shaped
-    (NBANDS, vector_len); ``stdict_all`` is None for ALPHA == 1.0, else keys "BB_<t>" + 'size').
-    """
+def prepare_job(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_list, NBANDS, freqlist, FREQ_BAND_TYPE, FILTER_TYPE,
+                FILTER_ORDER, FILTER_RIPPLE, rij=None, max_lag=-1, method=_capi.XCORR_AUTO):
+    """Host side of one driver call before the GPU runs: samples, time vector, co-array checks, job description."""
     data, Fs, tvec = as_record(st)
     nchan, npts = data.shape
     if rij is None:
@@ -74,11 +68,17 @@ def narrow_band_least_squares(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_lis
     if ALPHA != 1.0 and co.co_array_num < 4:
         raise RuntimeError('The co-array must have at least 4 elements for least trimmed squares. '
                            'Check rij array coordinates.')
-    eng = engine if engine is not None else default_engine()
     plan = build_plan(nchan, npts, Fs, co, WINLEN_list, WINOVER, ALPHA, NBANDS, freqlist, FREQ_BAND_TYPE,
                       FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE, max_lag=max_lag, method=method)
-    res = eng.run(plan, data, Results(plan, pinned=False, want_cmax=return_details))
+    if tvec is None:
+        tvec = np.arange(npts) / Fs / 86400.0
+    return data, tvec, co, plan
 
+
+def assemble_outputs(plan, res, tvec, co, WINLEN_list, WINOVER, ALPHA, NBANDS, w, h, freqlist, FREQ_BAND_TYPE,
+                     freq_resp_list, FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE):
+    """Results of one GPU job -> the reference's 9-tuple (narrow_band_least_squares.py:94-127)."""
+    Fs, npts, nchan = plan.fs, plan.npts, plan.nchan
     vector_len = max(reference_vector_len(npts, Fs, WINLEN_list, WINOVER), int(plan.win_count.max(initial=0)))
     vel_array, baz_array, mdccm_array, sig_tau_array, t_array = (np.full((NBANDS, vector_len), np.nan)
                                                                  for _ in range(5))
@@ -86,8 +86,6 @@ def narrow_band_least_squares(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_lis
     h_array = np.empty((NBANDS, len(h)), dtype=complex)
     stdict_all = None if ALPHA == 1.0 else {}
     num_compute_list = []
-    if tvec is None:
-        tvec = np.arange(npts) / Fs / 86400.0
     for ii in range(NBANDS):
         fmin, fmax = band_edges(freqlist, ii, FREQ_BAND_TYPE)
         sos = plot_sos(FILTER_TYPE, fmin, fmax, Fs, FILTER_ORDER, FILTER_RIPPLE)
@@ -105,7 +103,25 @@ def narrow_band_least_squares(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_lis
             sd = build_stdict(res.weights[r].T, t, co.idx, nchan)
             for key, val in sd.items():       # narrow_band_least_squares.py:116-124
                 stdict_all[key if key == 'size' else str(ii + 1).zfill(2) + '_' + key] = val
-    out = (vel_array, baz_array, mdccm_array, t_array, stdict_all, sig_tau_array, num_compute_list, w_array, h_array)
+    return (vel_array, baz_array, mdccm_array, t_array, stdict_all, sig_tau_array, num_compute_list, w_array, h_array)
+
+
+def narrow_band_least_squares(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_list, NBANDS, w, h, freqlist,
+                              FREQ_BAND_TYPE, freq_resp_list, FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE, *,
+                              rij=None, engine=None, max_lag=-1, method=_capi.XCORR_AUTO, return_details=False):
+    """Narrow-band least-squares array processing of ``st`` in ``NBANDS`` frequency bands.
+
+    Returns ``(vel_array, baz_array, mdccm_array, t_array, stdict_all, sig_tau_array,
+    num_compute_list, w_array, h_array)`` exactly like the reference (arrays shaped
+    (NBANDS, vector_len); ``stdict_all`` is None for ALPHA == 1.0, else keys "BB_<t>" + 'size').
+    """
+    data, tvec, co, plan = prepare_job(WINLEN_list, WINOVER, ALPHA, st, lat_list, lon_list, NBANDS, freqlist,
+                                       FREQ_BAND_TYPE, FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE, rij=rij,
+                                       max_lag=max_lag, method=method)
+    eng = engine if engine is not None else default_engine()
+    res = eng.run(plan, data, Results(plan, pinned=False, want_cmax=return_details))
+    out = assemble_outputs(plan, res, tvec, co, WINLEN_list, WINOVER, ALPHA, NBANDS, w, h, freqlist, FREQ_BAND_TYPE,
+                           freq_resp_list, FILTER_TYPE, FILTER_ORDER, FILTER_RIPPLE)
     if return_details:
         return out, plan, res
     return out

@@ -128,3 +128,73 @@ def gather_results(local: dict, counts, group=None):
         parts = [b[:totals[r]].cpu().numpy() for r, b in enumerate(bufs)]
         out[name] = merge_band_major(parts, all_counts)
     return out
+
+
+def all_shards(global_npts, win_len, win_hop, win_count, world, halo):
+    """Every rank's Shard — pure arithmetic, so each rank knows every other rank's window counts without a collective."""
+    return [Shard(global_npts, win_len, win_hop, win_count, r, world, halo) for r in range(world)]
+
+
+class PackedGather:
+    """The per-window estimates of every rank in ONE collective.
+
+    Each rank's libnbls outputs (mdccm, mad, vel, baz, sigma_tau, slowness) are written by the kernels straight into
+    one device block of 7 x e_max doubles (``outputs()`` hands libnbls the column pointers), so gathering is a single
+    ``all_gather_into_tensor`` of that block — no padding copies, no per-array calls, no host round trip — followed by
+    one index_select with a precomputed permutation into global band-major order (band after band, windows in time
+    order).  Integer lags and LTS weights ride in a second / third block only when asked for.  Window counts per rank
+    come from ``all_shards`` (no collective).  Works with NCCL (CUDA tensors) and gloo (CPU tensors; the CPU tests).
+    """
+
+    NCOL = 7      # mdccm, mad, vel, baz, sigma_tau, slowness[E][2]
+
+    def __init__(self, counts_per_rank, rank, npairs=0, want_lag=False, want_weights=False, device="cuda", group=None):
+        import torch
+        self.group, self.rank = group, rank
+        counts = np.asarray(counts_per_rank, dtype=np.int64)             # (world, B)
+        self.world, self.nbands = counts.shape
+        self.counts = counts
+        totals = counts.sum(axis=1)
+        self.e_local = int(totals[rank])
+        self.e_max = int(max(totals.max(), 1))
+        self.e_total = int(totals.sum())
+        offs = np.concatenate((np.zeros((self.world, 1), np.int64), np.cumsum(counts, axis=1)), axis=1)
+        idx = [r * self.e_max + offs[r, b] + np.arange(counts[r, b]) for b in range(self.nbands) for r in range(self.world)]
+        self.index = torch.as_tensor(np.concatenate(idx) if idx else np.zeros(0, np.int64), device=device)
+        self.local = torch.zeros((self.NCOL, self.e_max), dtype=torch.float64, device=device)
+        self.all = torch.empty((self.world, self.NCOL, self.e_max), dtype=torch.float64, device=device)
+        self.local_lag = self.all_lag = self.local_w = self.all_w = None
+        if want_lag:
+            self.local_lag = torch.zeros((self.e_max, npairs), dtype=torch.int32, device=device)
+            self.all_lag = torch.empty((self.world, self.e_max, npairs), dtype=torch.int32, device=device)
+        if want_weights:
+            self.local_w = torch.zeros((self.e_max, npairs), dtype=torch.uint8, device=device)
+            self.all_w = torch.empty((self.world, self.e_max, npairs), dtype=torch.uint8, device=device)
+
+    def outputs(self, lag_ptr=None, weights_ptr=None):
+        """_capi.Outputs whose members point into the packed block (device pointers for nbls_run_device)."""
+        from . import _capi
+        o = _capi.Outputs()
+        base, step = self.local.data_ptr(), 8 * self.e_max
+        o.mdccm, o.mad, o.vel, o.baz, o.sigma_tau, o.slowness = (base + i * step for i in range(6))
+        o.lag = self.local_lag.data_ptr() if self.local_lag is not None else lag_ptr
+        o.weights = self.local_w.data_ptr() if self.local_w is not None else weights_ptr
+        o.cmax = None
+        return o
+
+    def gather(self):
+        """-> dict of tensors in global band-major order on every rank (device-resident under NCCL)."""
+        import torch.distributed as dist
+        dist.all_gather_into_tensor(self.all.view(self.world * self.NCOL, self.e_max), self.local, group=self.group)
+        flat = self.all.permute(1, 0, 2).reshape(self.NCOL, self.world * self.e_max)
+        cols = flat[:5].index_select(1, self.index)
+        out = dict(zip(("mdccm", "mad", "vel", "baz", "sigma_tau"), cols))
+        slow = self.all[:, 5:7, :].reshape(self.world * self.e_max, 2)
+        out["slowness"] = slow.index_select(0, self.index)
+        if self.all_lag is not None:
+            dist.all_gather_into_tensor(self.all_lag.view(self.world * self.e_max, -1), self.local_lag, group=self.group)
+            out["lag"] = self.all_lag.reshape(self.world * self.e_max, -1).index_select(0, self.index)
+        if self.all_w is not None:
+            dist.all_gather_into_tensor(self.all_w.view(self.world * self.e_max, -1), self.local_w, group=self.group)
+            out["weights"] = self.all_w.reshape(self.world * self.e_max, -1).index_select(0, self.index)
+        return out

@@ -29,50 +29,17 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 
 
 def import_reference():
+    """The reference modules, imported from where they lie (oracle/refrun.py holds the shims)."""
+    sys.path.insert(0, ROOT)
+    from oracle import refrun
     if not os.path.isdir(REF):
         raise SystemExit(f"reference tree not found at {REF}")
-    stubs = os.path.join(HERE, "refstubs")
-    for p in (stubs, REF, os.path.join(REF, "lts_array")):
-        if p not in sys.path:
-            sys.path.insert(0, p)
-    # joblib/loky workers re-import: they inherit PYTHONPATH
-    os.environ["PYTHONPATH"] = os.pathsep.join([stubs, REF, os.path.join(REF, "lts_array"),
-                                               os.environ.get("PYTHONPATH", "")])
-    import lts_array  # noqa: F401
-    import helpers as ref_helpers
-    import narrow_band_least_squares as ref_nbls
-    from lts_array.classes import lts_classes as ref_cls
-    from lts_array.classes.lts_data_class import DataBin
-
-    class _NP:
-        """numpy proxy: only 'complex_' dtype strings are rewritten."""
-
-        def __getattr__(self, k):
-            return getattr(np, k)
-
-        @staticmethod
-        def _fix(kw):
-            if kw.get("dtype") == "complex_":
-                kw["dtype"] = np.complex128
-            return kw
-
-        def empty(self, *a, **k):
-            return np.empty(*a, **self._fix(k))
-
-        def zeros(self, *a, **k):
-            return np.zeros(*a, **self._fix(k))
-
-    ref_nbls.np = _NP()
-    return ref_helpers, ref_nbls, ref_cls, DataBin, lts_array.ltsva
+    return refrun.import_reference(REF)
 
 
 def make_stream(rec):
-    from obspy import Stream, Trace
-    st = Stream()
-    for i in range(rec.nchans):
-        st.append(Trace(rec.data[i].copy(), dict(sampling_rate=rec.fs, station=f"SYN{i + 1:02d}",
-                                                 location=f"{i + 1:02d}", starttime=rec.starttime)))
-    return st
+    from oracle import refrun
+    return refrun.make_stream(rec)
 
 
 def sha(a):

@@ -207,6 +207,54 @@ def test_gather_results_world2_gloo():
         assert np.array(got[rank]["lag"]).shape == (15, 5)
 
 
+def _gloo_packed_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        counts = [[3, 2, 0], [4, 2, 4]]                              # windows per band on rank 0 / rank 1
+        pg = sharding.PackedGather(counts, rank, npairs=5, want_lag=True, want_weights=True, device="cpu")
+        e, base = pg.e_local, 1000 * rank
+        o = pg.outputs()
+        assert o.vel == pg.local.data_ptr() + 2 * 8 * pg.e_max and o.slowness == pg.local.data_ptr() + 5 * 8 * pg.e_max
+        # what the kernels would write through those pointers: column arrays of e_local rows, slowness [e][2] interleaved
+        pg.local[2, :e] = base + torch.arange(e, dtype=torch.float64)
+        pg.local[5:7].reshape(-1)[:2 * e] = (base + torch.arange(e, dtype=torch.float64)).repeat_interleave(2) + \
+            torch.tensor([0.25, 0.5], dtype=torch.float64).repeat(e)
+        pg.local_lag[:e] = (base + torch.arange(e * 5, dtype=torch.int32)).reshape(e, 5)
+        pg.local_w[:e] = rank + 1
+        out = pg.gather()
+        q.put((rank, {k: v.tolist() for k, v in out.items()}))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_packed_gather_world2_gloo():
+    """One all_gather_into_tensor of the packed estimate block + a precomputed permutation = global band-major order."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_packed_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    r0 = np.arange(5, dtype=float); r1 = 1000 + np.arange(10, dtype=float)
+    exp = np.concatenate([r0[0:3], r1[0:4], r0[3:5], r1[4:6], r1[6:10]])
+    for rank in (0, 1):
+        assert np.array_equal(np.array(got[rank]["vel"]), exp)
+        sl = np.array(got[rank]["slowness"])
+        assert sl.shape == (15, 2) and np.array_equal(sl[:, 0], exp + 0.25) and np.array_equal(sl[:, 1], exp + 0.5)
+        lag = np.array(got[rank]["lag"])
+        assert lag.shape == (15, 5) and np.array_equal(lag[:, 0], 5 * exp - 4000 * (exp >= 1000))
+        assert np.array_equal(np.array(got[rank]["weights"])[:, 0], 1 + (exp >= 1000))
+
+
 @pytest.mark.parametrize("name", ["g1_ols_c4", "g2_lts_c6", "g4_lts_c12", "g5_ols_c5_overlap75", "g6_lts_c6_flip"])
 def test_slowness_ellipse_uncertainties_match_reference(name):
     """conf_int_vel / conf_int_baz (uncertainty.py) against the values the unmodified reference produced
@@ -315,3 +363,15 @@ def test_remove_elements_edits_the_callers_lists_like_the_reference():
         DataBin(10.0, 0.5, 1.0).build_data_arrays(stream_from_array(x[:4], 100.0), lat_all[:4], lon_all[:4],
                                                    remove_elements=[0, 1])
 
+
+
+def test_deal_arrays_by_array_then_segment():
+    """Config 5 sharding rule: arrays first, time segments only when ranks outnumber arrays."""
+    from narrow_band_least_squares_b200.batch import deal_arrays
+    items = deal_arrays(64, 8)
+    assert all(len(it) == 8 and all(s == 0 and g == 1 for _, s, g in it) for it in items)
+    assert sorted(a for it in items for a, _, _ in it) == list(range(64))
+    assert [a for a, _, _ in items[3]] == list(range(3, 64, 8))
+    items = deal_arrays(3, 8)                     # 8 ranks, 3 arrays: groups of 3, 3 and 2 ranks share an array by segment
+    assert [it[0] for it in items] == [(0, 0, 3), (0, 1, 3), (0, 2, 3), (1, 0, 3), (1, 1, 3), (1, 2, 3), (2, 0, 2), (2, 1, 2)]
+    assert deal_arrays(5, 1) == [[(a, 0, 1) for a in range(5)]]
