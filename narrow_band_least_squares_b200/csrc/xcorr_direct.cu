@@ -196,6 +196,171 @@ __global__ void __launch_bounds__(XC_MAX_WARPS * 32, 1) xcorr_direct_kernel(XcAr
     }
 }
 
+
+// ---- long windows ---------------------------------------------------------------------------
+// Windows too long for the kernel above (its shared memory grows with N: ~18 N bytes) are cut into tiles: a CTA owns
+// one (window, pair) and XL_LAGS consecutive lags, walks x_j in tiles of XL_TILE samples and keeps the matching
+// XL_TILE + XL_LAGS samples of x_i beside it (zero outside the window), so shared memory is constant in N.  A thread
+// owns 8 consecutive lags and slides a 16-value register window of x_i over the tile: 64 DFMA per 8 + 8 shared loads.
+// Per-CTA maxima go to a [item][lag block] table; xcorr_long_finish_kernel reduces them in rising-lag order (strict >,
+// so the first maximum wins like np.argmax) and normalises by the window energies.  Any N is served.
+constexpr int XL_THREADS = 256, XL_LAGS = XL_THREADS * 8, XL_TILE = 1024;
+
+struct XlArgs {
+    const double* y;
+    int64_t ldy;
+    int C, P, N, hop;
+    int64_t first;
+    int lag_max, nblk;        // lags -lag_max .. lag_max in nblk blocks of XL_LAGS
+    double* part_v;           // [W*P][nblk]
+    int* part_l;
+    int32_t* lag;
+    double* cmax;
+};
+
+__global__ void __launch_bounds__(XL_THREADS) xcorr_long_kernel(XlArgs g) {
+    __shared__ __align__(16) double sb[XL_TILE];
+    __shared__ __align__(16) double sa[(XL_TILE + XL_LAGS + 8) / 8 * 10];      // rows of 8 padded to 10 (pad_b)
+    __shared__ double red_v[XL_THREADS / 32];
+    __shared__ int red_l[XL_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t item = blockIdx.x / g.nblk;
+    const int blk = blockIdx.x - (int)(item * g.nblk);
+    const int w = (int)(item / g.P), p = (int)(item - (int64_t)w * g.P);
+    int ci = 0, rem = p;
+    while (rem >= g.C - 1 - ci) { rem -= g.C - 1 - ci; ++ci; }
+    const int cj = ci + 1 + rem;
+    const int64_t t0 = g.first + (int64_t)w * g.hop;
+    const double* xa = g.y + (int64_t)ci * g.ldy + t0;
+    const double* xb = g.y + (int64_t)cj * g.ldy + t0;
+    const int N = g.N;
+    const int k_lo = -g.lag_max + blk * XL_LAGS;          // first lag of the block
+    const int k0 = k_lo + tid * 8;                        // this thread's lags k0 .. k0+7
+    double acc[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) acc[r] = 0.0;
+    // c[k] = sum_n a[n+k] b[n]: only tiles of b whose shifted range meets [0, N) for some lag of the block matter
+    const int n_first = max(0, -(k_lo + XL_LAGS - 1)), n_last = min(N, N - k_lo);      // n in [n_first, n_last)
+    for (int nt = n_first / XL_TILE * XL_TILE; nt < n_last; nt += XL_TILE) {
+        __syncthreads();
+        for (int e = tid; e < XL_TILE; e += XL_THREADS) sb[e] = (nt + e < N) ? xb[nt + e] : 0.0;
+        for (int e = tid; e < XL_TILE + XL_LAGS + 8; e += XL_THREADS) {
+            const int64_t ia = (int64_t)nt + k_lo + e;
+            sa[pad_b(e)] = (ia >= 0 && ia < N) ? xa[ia] : 0.0;
+        }
+        __syncthreads();
+        const double* pa = sa + tid * 10;                 // a[nt + k0 + 8 m + q] = pa[10 m + q]: conflict-free LDS.128
+        double aw[16];
+        {
+            const double2* q2 = reinterpret_cast<const double2*>(pa);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) { const double2 d = q2[q]; aw[2 * q] = d.x; aw[2 * q + 1] = d.y; }
+        }
+        for (int n = 0; n < XL_TILE; n += 8) {
+            double bv[8];
+            const double2* a2 = reinterpret_cast<const double2*>(pa + (n / 8 + 1) * 10);
+            const double2* b2 = reinterpret_cast<const double2*>(sb + n);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double2 d = a2[q]; aw[8 + 2 * q] = d.x; aw[9 + 2 * q] = d.y;
+                const double2 e = b2[q]; bv[2 * q] = e.x; bv[2 * q + 1] = e.y;
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) acc[r] = fma(aw[r + q], bv[q], acc[r]);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) aw[q] = aw[8 + q];
+        }
+    }
+    Best best;
+    best.v = -DBL_MAX;
+    best.lag = INT_MAX;
+#pragma unroll
+    for (int r = 0; r < 8; ++r)
+        if (k0 + r <= g.lag_max) best_update(best, acc[r], k0 + r);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        Best other;
+        other.v = __shfl_xor_sync(0xffffffffu, best.v, o);
+        other.lag = __shfl_xor_sync(0xffffffffu, best.lag, o);
+        best_update(best, other.v, other.lag);
+    }
+    if (lane == 0) { red_v[warp] = best.v; red_l[warp] = best.lag; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int i = 1; i < XL_THREADS / 32; ++i) best_update(best, red_v[i], red_l[i]);
+        g.part_v[item * g.nblk + blk] = best.v;
+        g.part_l[item * g.nblk + blk] = best.lag;
+    }
+}
+
+__global__ void __launch_bounds__(256) xcorr_long_finish_kernel(XlArgs g) {
+    __shared__ double red_e[2][8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t item = blockIdx.x;
+    const int w = (int)(item / g.P), p = (int)(item - (int64_t)w * g.P);
+    int ci = 0, rem = p;
+    while (rem >= g.C - 1 - ci) { rem -= g.C - 1 - ci; ++ci; }
+    const int cj = ci + 1 + rem;
+    const int64_t t0 = g.first + (int64_t)w * g.hop;
+    const double* xa = g.y + (int64_t)ci * g.ldy + t0;
+    const double* xb = g.y + (int64_t)cj * g.ldy + t0;
+    double ea = 0.0, eb = 0.0;
+    for (int e = tid; e < g.N; e += 256) {
+        ea = fma(xa[e], xa[e], ea);
+        eb = fma(xb[e], xb[e], eb);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        ea += __shfl_xor_sync(0xffffffffu, ea, o);
+        eb += __shfl_xor_sync(0xffffffffu, eb, o);
+    }
+    if (lane == 0) { red_e[0][warp] = ea; red_e[1][warp] = eb; }
+    __syncthreads();
+    if (tid == 0) {
+        double Ea = 0.0, Eb = 0.0;
+        for (int i = 0; i < 8; ++i) { Ea += red_e[0][i]; Eb += red_e[1][i]; }
+        Best best;
+        best.v = -DBL_MAX;
+        best.lag = INT_MAX;
+        for (int b = 0; b < g.nblk; ++b) best_update(best, g.part_v[item * g.nblk + b], g.part_l[item * g.nblk + b]);
+        const double den = sqrt(Ea * Eb);
+        // zero-energy pair: cij is all-NaN, np.argmax gives index 0 = the lowest lag searched (lts_classes.py:871-875)
+        const bool dead = !(den > 0.0) || best.lag == INT_MAX;
+        g.lag[item] = dead ? -g.lag_max : best.lag;
+        if (g.cmax) g.cmax[item] = dead ? __longlong_as_double(0x7ff8000000000000LL) : best.v / den;
+    }
+}
+
+static int xcorr_long_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
+                           int lag_max, int32_t* lag, double* cmax) {
+    const int P = C * (C - 1) / 2;
+    XlArgs a;
+    memset(&a, 0, sizeof(a));
+    a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first; a.lag_max = lag_max;
+    a.nblk = (2 * lag_max + 1 + XL_LAGS - 1) / XL_LAGS;
+    // windows per launch bounded so that the partial table and the grid stay small
+    const int64_t per_win = (int64_t)P * a.nblk;
+    const int wb = (int)std::max<int64_t>(1, std::min<int64_t>(W, (1LL << 26) / per_win));
+    NBLS_CHECK(ensure(ctx, ctx->scratch, (size_t)wb * per_win * (sizeof(double) + sizeof(int)) + 256));
+    a.part_v = (double*)ctx->scratch.p;
+    a.part_l = (int*)(a.part_v + (size_t)wb * per_win);
+    for (int w0 = 0; w0 < W; w0 += wb) {
+        const int wn = std::min(wb, W - w0);
+        a.first = first + (int64_t)w0 * hop;
+        a.lag = lag + (int64_t)w0 * P;
+        a.cmax = cmax ? cmax + (int64_t)w0 * P : nullptr;
+        KernelGroupScope ks(ctx, KG_DIRECT, (double)wn * P * 2.0 * (double)N * (double)N);
+        xcorr_long_kernel<<<(unsigned)(wn * per_win), XL_THREADS, 0, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        xcorr_long_finish_kernel<<<(unsigned)(wn * P), 256, 0, ctx->stream>>>(a);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 2;
+    }
+    return NBLS_OK;
+}
+
 // list == nullptr: every (window, pair) of the band.  Otherwise only the items w*P+p in list[0..*count)
 // (both on the device; used by the FFT path to settle near-tied arg-maxima), with at most `grid_cap` CTAs.
 int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,
@@ -218,9 +383,9 @@ int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, in
     const int nwarps = (a.nitems + rounds - 1) / rounds;
     const size_t smem = ((size_t)a.M + 8 + (size_t)a.M / 8 * 10) * sizeof(double);
     if (smem > ctx->smem_optin - 1024) {
-        set_error("nbls_xcorr(direct): window of %d samples needs %zu B of shared memory (> %zu)", N, smem,
-                  ctx->smem_optin - 1024);
-        return NBLS_ERR_UNSUPPORTED;
+        // the window does not fit in one SM's shared memory: tiled kernel (any N)
+        NBLS_REQUIRE(!list, "nbls_xcorr(direct): list mode is not available for windows of %d samples", N);
+        return xcorr_long_band(ctx, yband, ldy, C, N, hop, first, W, a.lag_max, lag, cmax);
     }
     NBLS_CUDA(allow_max_dynamic_smem(xcorr_direct_kernel, ctx->smem_optin));
     const int64_t nblocks = list ? std::min<int64_t>((int64_t)W * P, std::max(1, grid_cap)) : (int64_t)W * P;

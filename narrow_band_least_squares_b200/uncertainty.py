@@ -14,11 +14,13 @@ The geometry is solved directly instead of through quartic roots:
 * ``conf_int_baz`` = half the angle between the two tangent rays from the origin — a homogeneous
   quadratic in the ray direction, solved in closed form.
 
-Where the reference's closed-form machinery is stable (origin outside the ellipse, which is every
-window with a usable estimate) both give the same numbers to ~1e-9; if the origin lies inside the
-ellipse no tangent exists, every azimuth is inside the confidence region, and this module reports
-``conf_int_baz = 180`` and ``conf_int_vel = inf`` (the reference returns the real part of complex
-roots there, which has no geometric meaning).
+Where the origin lies outside the ellipse (every window with a usable estimate) this and the reference's
+closed-form machinery give the same numbers to ~1e-9.  If the origin lies INSIDE the ellipse no tangent exists;
+the reference then still returns numbers — the tangency quadratic of ``rthEllipse`` (lts_classes.py:617-633) has
+complex roots and it keeps their real parts, and the extremal distances (:588-615) stay real — so for identical
+results ``_tangent_half_angle_inside`` evaluates that same quadratic in complex arithmetic and keeps the real
+parts, and ``conf_int_vel`` uses the (finite) extremal distances.  NBLS itself discards both outputs
+(narrow_band_least_squares.py:91).
 """
 from __future__ import annotations
 
@@ -95,6 +97,39 @@ def _tangent_half_angle(a, b, x0, y0):
     return np.where(e > 0, 0.5 * diff, 180.0), e
 
 
+def _tangent_half_angle_inside(a, b, x0, y0):
+    """conf_int_baz (degrees) the reference returns when the origin lies inside the ellipse: the tangency conditions of
+    rthEllipse (lts_classes.py:561-568 constants, :617-633) solved over the complex numbers, real parts kept.
+
+    With the ellipse axis-aligned, G = 1/a^2, H = 1/b^2, B = 2 x0/a^2, D = 2 y0/b^2, E = x0^2/a^2 + y0^2/b^2 - 1, the
+    tangent points (x, y) satisfy  (D^2 + B^2 H/G) y'^2 + 4 D E y' + (4 E^2 - B^2 E/G) = 0,  y = -y',
+    x = +-sqrt(E/G - (H/G) y^2); E < 0 inside, so the discriminant is negative and the roots are complex conjugates.
+    """
+    G, H = 1.0 / (a * a), 1.0 / (b * b)
+    B, D = 2.0 * x0 * G, 2.0 * y0 * H
+    E = 0.5 * (B * x0 + D * y0) - 1.0
+    qa = D * D + B * B * H / G
+    qb = 4.0 * D * E
+    qc = 4.0 * E * E - B * B * E / G
+    disc = np.sqrt((qb * qb - 4.0 * qa * qc).astype(np.complex128))
+    # the numerically stable pair of roots (Numerical Recipes 5.6, as quadraticEqn :438-457): q/a and c/q
+    with np.errstate(divide="ignore", invalid="ignore"):
+        q = np.where(qb != 0, -0.5 * (qb + np.sign(qb) * disc), -np.sqrt((-qa * qc).astype(np.complex128)))
+        r0, r1 = q / qa, qc / q
+        ys = [-r0, -r1]
+        xs = [np.sqrt(E / G - (H / G) * y * y) for y in ys]
+    neg = x0 < 0
+    xs = [np.where(neg, -x, x) for x in xs]
+    ex = [np.real(x) for x in xs]
+    ey = [np.real(y) for y in ys]
+    flip = (x0 == 0) | (np.abs(x0) - a < 0)           # "various quadrant fixes" (:631-632): first tangent point mirrored
+    ex[0] = np.where(flip, -ex[0], ex[0])
+    ang = [(np.degrees(np.arctan2(y, x)) - 360.0) % 360.0 for x, y in zip(ex, ey)]
+    d = np.abs(ang[1] - ang[0])
+    d = np.where(d > 180.0, np.abs(d - 360.0), d)
+    return 0.5 * d
+
+
 def slowness_ellipse_ci(slowness, sigma_tau, xij, weights=None, p=0.90):
     """conf_int_vel, conf_int_baz for W windows.
 
@@ -129,6 +164,10 @@ def slowness_ellipse_ci(slowness, sigma_tau, xij, weights=None, p=0.90):
     dmin, dmax = _extremal_distances(a, b, x0, y0)
     with np.errstate(divide="ignore"):
         vel_ci = 0.5 * np.abs(1.0 / dmin - 1.0 / dmax)
-    civ[i] = np.where(e > 0, vel_ci, np.inf)
+    civ[i] = vel_ci
+    inside = ~(e > 0)
+    if inside.any():
+        half = half.copy()
+        half[inside] = _tangent_half_angle_inside(a[inside], b[inside], x0[inside], y0[inside])
     cib[i] = half
     return civ, cib

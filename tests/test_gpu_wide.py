@@ -233,3 +233,26 @@ def test_batch_equals_standalone_runs(eng):
                 assert set(out[4]) == set(ref[4]) and len(out[4]) > 1
                 for key in ref[4]:
                     assert np.array_equal(out[4][key], ref[4][key]), (a, key)
+
+
+# ---------------------------------------------------------------------------------------------
+# long windows: any window length is served; beyond the FFT plans the time-domain kernels take over
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,max_lag", [(8192, -1), (13000, -1), (20000, -1), (20000, 700)])
+def test_long_windows_match_oracle(eng, n, max_lag):
+    """N = 8192 (beyond the 12288-point FFT plans: shared-memory time-domain kernel), N = 13000 and 20000 (200 s at
+    100 sps, the reference example's FMIN = 0.1 Hz band: tiled time-domain kernel) against np.correlate + argmax."""
+    fs = 100.0
+    rec = plane_wave_record(seed=50 + n % 7, nchans=4, npts=n * 2 + 500, fs=fs, aperture_km=0.6, noise_every_min=0)
+    sos = [orc.design_sos("butter", 0.1, 0.2, fs, 2)]
+    filt = eng.filter_bands(rec.data, fs, sos)
+    filt[0, 2, :] = 0.0 if n == 13000 else filt[0, 2, :]          # a dead channel on one case
+    hop = n // 2
+    starts = np.arange(0, rec.npts - n, hop)
+    pairs, _, _, _ = orc.co_array(rec.rij)
+    lag, cmax, *_ = orc.correlate_windows(np.ascontiguousarray(filt[0].T), starts, n, fs, pairs,
+                                          max_lag=None if max_lag < 0 else max_lag)
+    for method in (_capi.XCORR_AUTO, _capi.XCORR_DIRECT):
+        got_lag, got_cmax = eng.xcorr(filt, [n], [hop], [len(starts)], max_lag=max_lag, method=method)
+        assert np.array_equal(got_lag.T, lag), (n, method)
+        assert np.allclose(got_cmax.T, cmax, rtol=0, atol=1e-12, equal_nan=True), (n, method)
