@@ -252,6 +252,16 @@ int nbls_measure_fp64_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
 /* The same with FP32 FMAs (roofline denominator of the FP32 screening FFTs). */
 int nbls_measure_fp32_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
 
+/* ---- experiment: tensor-core DFT pass ("tensor-pipe verdict") ---------------------------
+ * Runs `reps` radix-32 passes (32-point inverse DFT of every row + inter-pass twiddles) over x_dev [rows][32] complex
+ * FP32 -> y_dev, tile by tile in shared memory, `iters` times, and returns the best launch time.
+ *   mode 0: the production way - register butterflies on the CUDA cores (fft_radix.cuh)
+ *   mode 1: tcgen05.mma DFT-matrix product, FP16 operands, one product  (error ~2^-11)
+ *   mode 2: the same with split FP16 operands, three products           (error ~2^-21, FP32-grade)
+ * Not used by any production path; kept so that the verdict can be re-measured. */
+int nbls_experiment_dft_pass(nbls_ctx* ctx, int32_t mode, const float* x_dev, int64_t rows, int32_t reps, int32_t iters,
+                             float* y_dev, float* ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -98,6 +98,8 @@ EXPORTS = {
     "nbls_mark": (C.c_int, [C.c_void_p, C.c_int32]),
     "nbls_mark_elapsed": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "nbls_launch_count": (C.c_int64, [C.c_void_p]),
+    "nbls_experiment_dft_pass": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
+                                           C.POINTER(C.c_float)]),
     "nbls_measure_fp64_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
     "nbls_measure_fp32_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
 }

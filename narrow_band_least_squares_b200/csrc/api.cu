@@ -629,6 +629,13 @@ int nbls_measure_fp64_peak(nbls_ctx* ctx, int32_t iters, double* tflops) {
     return fp64_peak_impl(ctx, iters, tflops);
 }
 
+int nbls_experiment_dft_pass(nbls_ctx* ctx, int32_t mode, const float* x_dev, int64_t rows, int32_t reps, int32_t iters,
+                             float* y_dev, float* ms) {
+    NBLS_REQUIRE(ctx, "nbls_experiment_dft_pass: null context");
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    return experiment_dft_pass_impl(ctx, mode, x_dev, rows, reps, iters, y_dev, ms);
+}
+
 int nbls_measure_fp32_peak(nbls_ctx* ctx, int32_t iters, double* tflops) {
     NBLS_REQUIRE(ctx, "nbls_measure_fp32_peak: null context");
     NBLS_CUDA(cudaSetDevice(ctx->device));

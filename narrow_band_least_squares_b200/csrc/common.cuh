@@ -136,6 +136,8 @@ int xcorr_impl(nbls_ctx* ctx, const nbls_window_desc* w, const double* y, int C,
                int64_t ystride_band, int32_t* lag, double* cmax);
 int solve_impl(nbls_ctx* ctx, const nbls_solve_desc* s, int64_t nwin, const int32_t* lag,
                const double* cmax, const nbls_outputs* out);
+int experiment_dft_pass_impl(nbls_ctx* ctx, int mode, const float* x_dev, int64_t rows, int reps, int iters, float* y_dev,
+                             float* ms_out);
 int fp64_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
 int fp32_peak_impl(nbls_ctx* ctx, int iters, double* tflops);
 int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N, int hop, int64_t first, int W,

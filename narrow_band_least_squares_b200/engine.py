@@ -250,6 +250,22 @@ class Engine:
         """nbls_solve on device-resident lags / cmax with ``plan``'s solver description; asynchronous."""
         check(self.lib.nbls_solve(self.ctx, C.byref(plan.job.solve), int(nwin), lag_ptr, cmax_ptr, C.byref(out_struct)))
 
+    def experiment_dft_pass(self, x, mode, reps=1, iters=3):
+        """Tensor-pipe experiment (nbls_experiment_dft_pass): x (rows, 32) complex64 -> (y (rows, 32) complex64, ms)."""
+        x = np.ascontiguousarray(x, dtype=np.complex64)
+        rows = x.shape[0]
+        xd = DeviceArray(self, x.nbytes).upload(x)
+        yd = DeviceArray(self, x.nbytes)
+        ms = C.c_float()
+        try:
+            check(self.lib.nbls_experiment_dft_pass(self.ctx, int(mode), xd.ptr, rows, int(reps), int(iters), yd.ptr,
+                                                    C.byref(ms)))
+            self.synchronize()
+            y = yd.download(x.shape, np.complex64)
+        finally:
+            xd.free(); yd.free()
+        return y, float(ms.value)
+
     def launch_count(self):
         return int(self.lib.nbls_launch_count(self.ctx))
 
