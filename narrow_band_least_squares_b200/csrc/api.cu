@@ -176,14 +176,18 @@ static int run_device_inner(nbls_ctx* ctx, const nbls_job* job, const double* x,
     NBLS_REQUIRE(out && out->lag, "nbls_run: outputs.lag is required");
     const int64_t ldy = round_up(T, 16);
     // band groups bounded by the workspace limit
-    size_t freeb = 0, totalb = 0;
-    NBLS_CUDA(cudaMemGetInfo(&freeb, &totalb));
-    size_t limit = ctx->ws_limit ? ctx->ws_limit : (size_t)((double)(freeb + ctx->filt.cap) * 0.8);
     const size_t per_band = (size_t)C * ldy * sizeof(double);
-    int G = (int)std::min<size_t>((size_t)B, std::max<size_t>(1, limit / per_band));
-    if ((size_t)G * per_band > freeb + ctx->filt.cap) {
-        set_error("nbls_run: one band of filtered data (%zu B) does not fit in device memory", per_band);
-        return NBLS_ERR_NOMEM;
+    int G = B;
+    // the free-memory query costs ~1 ms of idle GPU: skipped when the workspace of an earlier call already holds every band
+    if ((size_t)B * per_band > ctx->filt.cap || (ctx->ws_limit && (size_t)B * per_band > ctx->ws_limit)) {
+        size_t freeb = 0, totalb = 0;
+        NBLS_CUDA(cudaMemGetInfo(&freeb, &totalb));
+        size_t limit = ctx->ws_limit ? ctx->ws_limit : (size_t)((double)(freeb + ctx->filt.cap) * 0.8);
+        G = (int)std::min<size_t>((size_t)B, std::max<size_t>(1, limit / per_band));
+        if ((size_t)G * per_band > freeb + ctx->filt.cap) {
+            set_error("nbls_run: one band of filtered data (%zu B) does not fit in device memory", per_band);
+            return NBLS_ERR_NOMEM;
+        }
     }
     NBLS_CHECK(ensure(ctx, ctx->filt, (size_t)G * per_band));
     double* yf = (double*)ctx->filt.p;
@@ -193,7 +197,8 @@ static int run_device_inner(nbls_ctx* ctx, const nbls_job* job, const double* x,
         cmax = (double*)ctx->cmaxbuf.p;
     }
     float ms_f = 0, ms_x = 0;
-    cudaEvent_t ea = ctx->ev[EV_START], eb = ctx->ev[EV_FILTER], ec = ctx->ev[EV_XCORR];
+    // band-grouped runs time every group with the profile event pair + EV_FILTER (EV_START must keep the run's start)
+    cudaEvent_t ea = ctx->pev[0], eb = ctx->ev[EV_FILTER], ec = ctx->ev[EV_XCORR];
     int64_t row = 0;
     const bool grouped = G < B;
     for (int b0 = 0; b0 < B; b0 += G) {

@@ -109,6 +109,8 @@ struct nbls_ctx {
     double prof_work[nbls::KG_COUNT] = {};
     double audit_err = 0.0;                 // NBLS_OPT_SCREEN_AUDIT: largest |FP32 - FP64| over every searched lag
     int64_t audit_lags = 0;
+    std::vector<unsigned char> filter_key;  // host image of the filter tables now on the device (filter.cu)
+    const void *filter_key_coef = nullptr, *filter_key_taper = nullptr;
     int64_t last_E = -1, last_P = 0;        // rows / pairs of the lags kept by the last nbls_run_host (nbls_resolve_host)
     int64_t ts_redone_pairs = 0;            // two-stage: pair-windows redone over all lags
 };

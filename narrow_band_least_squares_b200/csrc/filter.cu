@@ -608,21 +608,40 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     double* dcoef = (double*)ctx->coef.p;
     double* dml = dcoef + n_coef;
     int* dproc = (int*)(dml + n_ml);
-    NBLS_CUDA(cudaMemcpyAsync(dcoef, hbuf.data(), hbuf.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-    NBLS_CUDA(cudaMemcpyAsync(dproc, hproc.data(), B * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-    // pageable sources: the copies above are staged before returning, but be explicit
-    NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-
+    // The device copies of the tables are kept between calls: a caller that repeats a job (a queue of records with one
+    // band plan) pays the two uploads and their synchronisations - a few hundred microseconds of idle GPU - only once.
+    std::vector<unsigned char> key(hbuf.size() * sizeof(double) + hproc.size() * sizeof(int) + 2 * d->taper_len * sizeof(double));
+    {
+        unsigned char* kp = key.data();
+        memcpy(kp, hbuf.data(), hbuf.size() * sizeof(double)); kp += hbuf.size() * sizeof(double);
+        memcpy(kp, hproc.data(), hproc.size() * sizeof(int)); kp += hproc.size() * sizeof(int);
+        if (d->taper_len > 0) {
+            memcpy(kp, d->taper_up, d->taper_len * sizeof(double)); kp += d->taper_len * sizeof(double);
+            memcpy(kp, d->taper_down, d->taper_len * sizeof(double));
+        }
+    }
+    const bool cached = ctx->filter_key == key && ctx->filter_key_coef == ctx->coef.p &&
+                        (d->taper_len == 0 || ctx->filter_key_taper == ctx->taper.p);
     const double *dup = nullptr, *ddown = nullptr;
-    if (d->taper_len > 0) {
-        NBLS_CHECK(ensure(ctx, ctx->taper, 2 * d->taper_len * sizeof(double)));
-        double* tp = (double*)ctx->taper.p;
-        NBLS_CUDA(cudaMemcpyAsync(tp, d->taper_up, d->taper_len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-        NBLS_CUDA(cudaMemcpyAsync(tp + d->taper_len, d->taper_down, d->taper_len * sizeof(double),
-                                  cudaMemcpyHostToDevice, ctx->stream));
+    if (d->taper_len > 0) NBLS_CHECK(ensure(ctx, ctx->taper, 2 * d->taper_len * sizeof(double)));
+    if (!cached || (d->taper_len > 0 && ctx->filter_key_taper != ctx->taper.p)) {
+        NBLS_CUDA(cudaMemcpyAsync(dcoef, hbuf.data(), hbuf.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        NBLS_CUDA(cudaMemcpyAsync(dproc, hproc.data(), B * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        if (d->taper_len > 0) {
+            double* tp = (double*)ctx->taper.p;
+            NBLS_CUDA(cudaMemcpyAsync(tp, d->taper_up, d->taper_len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+            NBLS_CUDA(cudaMemcpyAsync(tp + d->taper_len, d->taper_down, d->taper_len * sizeof(double),
+                                      cudaMemcpyHostToDevice, ctx->stream));
+        }
+        // pageable sources: wait until the copies have left the host buffers
         NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-        dup = tp;
-        ddown = tp + d->taper_len;
+        ctx->filter_key.swap(key);
+        ctx->filter_key_coef = ctx->coef.p;
+        ctx->filter_key_taper = d->taper_len > 0 ? ctx->taper.p : nullptr;
+    }
+    if (d->taper_len > 0) {
+        dup = (const double*)ctx->taper.p;
+        ddown = dup + d->taper_len;
     }
     double* dstate = nullptr;
     if (nchunks > 1) {

@@ -49,6 +49,32 @@ struct Sums {
     double sxx, sxy, syy, sxt, syt, obj;
 };
 
+// The six sums of a ranking pass reduced over the warp with 8 exchanges instead of 30: at the xor-16 step a lane keeps
+// three of the six values and hands the other three to its partner, then two of (three + a zero), then one; the last two
+// steps are plain butterflies.  Every partial sum adds the same two operands as warp_sum()'s butterfly does (a + b = b + a
+// exactly), so the totals - read back from lanes 0, 4, 8, 16, 20, 24 - are bit-identical to six warp_sum() calls.
+__device__ __forceinline__ void warp_sum6(Sums& s, int lane) {
+    const bool u16 = (lane & 16) != 0, u8 = (lane & 8) != 0, u4 = (lane & 4) != 0;
+    double k0 = u16 ? s.sxt : s.sxx, k1 = u16 ? s.syt : s.sxy, k2 = u16 ? s.obj : s.syy;      // kept: v0 v1 v2 | v3 v4 v5
+    const double g0 = u16 ? s.sxx : s.sxt, g1 = u16 ? s.sxy : s.syt, g2 = u16 ? s.syy : s.obj;
+    k0 += __shfl_xor_sync(0xffffffffu, g0, 16);
+    k1 += __shfl_xor_sync(0xffffffffu, g1, 16);
+    k2 += __shfl_xor_sync(0xffffffffu, g2, 16);
+    // four slots (k0 k1 | k2 0): lanes with bit 3 clear keep the first two
+    double m0 = u8 ? k2 : k0, m1 = u8 ? 0.0 : k1;
+    const double h0 = u8 ? k0 : k2, h1 = u8 ? k1 : 0.0;
+    m0 += __shfl_xor_sync(0xffffffffu, h0, 8);
+    m1 += __shfl_xor_sync(0xffffffffu, h1, 8);
+    double t = u4 ? m1 : m0;
+    const double h = u4 ? m0 : m1;
+    t += __shfl_xor_sync(0xffffffffu, h, 4);
+    t += __shfl_xor_sync(0xffffffffu, t, 2);
+    t += __shfl_xor_sync(0xffffffffu, t, 1);
+    // value index -> lanes: v0 0-3, v1 4-7, v2 8-11, v3 16-19, v4 20-23, v5 24-27
+    s.sxx = __shfl_sync(0xffffffffu, t, 0);  s.sxy = __shfl_sync(0xffffffffu, t, 4);  s.syy = __shfl_sync(0xffffffffu, t, 8);
+    s.sxt = __shfl_sync(0xffffffffu, t, 16); s.syt = __shfl_sync(0xffffffffu, t, 20); s.obj = __shfl_sync(0xffffffffu, t, 24);
+}
+
 // 2x2 normal equations -> coefficients; singular systems give NaN (never selected)
 __device__ __forceinline__ void solve2(const Sums& s, double& zx, double& zy) {
     const double det = s.sxx * s.syy - s.sxy * s.sxy;
@@ -78,8 +104,7 @@ __device__ __forceinline__ Sums rank_pass(const double* x0, const double* x1, co
         }
     }
     __syncwarp();
-    s.sxx = warp_sum(s.sxx); s.sxy = warp_sum(s.sxy); s.syy = warp_sum(s.syy);
-    s.sxt = warp_sum(s.sxt); s.syt = warp_sum(s.syt); s.obj = warp_sum(s.obj);
+    warp_sum6(s, lane);
     return s;
 }
 
@@ -92,7 +117,8 @@ __device__ __forceinline__ Sums rank_pass(const double* x0, const double* x1, co
 // ranked with the exact FP64 rule.  The subset, and hence the sums, are identical to rank_pass's.
 template <int NI>
 __device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, const double* y, double* absr,
-                                            __half2* key2, int P, int h, double zx, double zy, int lane) {
+                                            __half2* key2, int P, int h, double zx, double zy, int lane,
+                                            unsigned (&member)[NI > 0 ? NI : 1]) {
     __half* key = reinterpret_cast<__half*>(key2);
     const unsigned short* keyb = reinterpret_cast<const unsigned short*>(key2);
     const __half hnan = __ushort_as_half((unsigned short)0x7E00);
@@ -157,6 +183,7 @@ __device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, 
 #pragma unroll
     for (int i = 0; i < NI; ++i) {
         const int p = lane + 32 * i;
+        member[i] = __ballot_sync(0xffffffffu, in[i]);      // the h-subset as NI lane masks (warp-uniform)
         if (in[i]) {
             const double a = x0[p], b = x1[p], t = y[p];
             s.sxx = fma(a, a, s.sxx); s.sxy = fma(a, b, s.sxy); s.syy = fma(b, b, s.syy);
@@ -165,30 +192,39 @@ __device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, 
         }
     }
     __syncwarp();
-    s.sxx = warp_sum(s.sxx); s.sxy = warp_sum(s.sxy); s.syy = warp_sum(s.syy);
-    s.sxt = warp_sum(s.sxt); s.syt = warp_sum(s.syt); s.obj = warp_sum(s.obj);
+    warp_sum6(s, lane);
     return s;
 }
 
 template <int NI>
 __device__ __forceinline__ Sums rank_any(const double* x0, const double* x1, const double* y, double* absr, __half2* key2,
-                                         int P, int h, double zx, double zy, int lane) {
+                                         int P, int h, double zx, double zy, int lane, unsigned (&member)[NI > 0 ? NI : 1]) {
     if constexpr (NI == 0) return rank_pass(x0, x1, y, absr, P, h, zx, zy, lane);
-    else return rank_pass16<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
+    else return rank_pass16<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane, member);
 }
 
 // C-steps from (zx, zy) until the objective repeats or `limit` steps (:89-103 / :125-139)
 template <int NI>
 __device__ __forceinline__ void csteps(const double* x0, const double* x1, const double* y, double* absr, __half2* key2,
                                        int P, int h, int limit, double& zx, double& zy, double& obj, int lane) {
-    Sums s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
+    unsigned was[NI > 0 ? NI : 1], now[NI > 0 ? NI : 1];
+    Sums s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane, was);
     double prev = 0.0;
     obj = s.obj;
     for (int kk = 0; kk < limit; ++kk) {
         solve2(s, zx, zy);
-        s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane);
+        s = rank_any<NI>(x0, x1, y, absr, key2, P, h, zx, zy, lane, now);
         obj = s.obj;
         if (kk >= 1 && obj == prev) break;
+        if constexpr (NI > 0) {
+            // The h-subset did not change: the next step would refit the same rows - the same sums, hence (zx, zy) and
+            // the objective bit for bit - and then stop on the repeated objective (or on the step limit).  Stop here with
+            // exactly those values and save the ranking pass.
+            bool same = true;
+#pragma unroll
+            for (int i = 0; i < NI; ++i) { same = same && (now[i] == was[i]); was[i] = now[i]; }
+            if (same) break;
+        }
         prev = obj;
     }
 }

@@ -79,8 +79,9 @@ struct XfArgs {
     int k0;               // stage A: lag bound of the search (>= 0); otherwise -1
     int lag_dead;         // lag written for a zero-energy pair: -(N-1) or -max_lag of the request
     double* part;         // stage A: [wn][C][2] = sum of x^2 over n < N-k0-1 (head) and over n > k0 (tail)
-    int* pf_list;         // stage A out: batch items wl*P+p whose proof failed (unordered; the host sorts them)
-    int* pf_count;
+    int* pf_list;         // stage B in: batch items wl*P+p whose proof failed, ascending (xf_compact_* kernels)
+    int* pf_count;        // [0] number of such items, [1] number of windows holding at least one
+    unsigned char* pf_flag;   // stage A out: [wn*P] 1 = the proof failed for batch item wl*P+p
     const int* wlist;     // window-list mode: band-level window index of launch slot s; nullptr = w0 + s
     const int* items;     // item mode (pair kernel, xf_verify_items_kernel): sorted batch items wl*P+p, two per pair CTA
     int n_items;
@@ -853,7 +854,7 @@ __global__ void __launch_bounds__(NW * 32, 32 / NW) xf_verify_kernel(XfArgs g) {
             const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
             const double* pj = g.part + ((int64_t)wl * g.C + j) * 2;
             const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
-            if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.pf_list[atomicAdd(g.pf_count, 1)] = wl * g.P + p;
+            if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.pf_flag[(int64_t)wl * g.P + p] = 1;
         }
         // consistency guard: the exact maximum must sit where the screen saw it
         const float ee = fabsf((float)(c - (double)g.sval[(int64_t)wl * g.P + p]));
@@ -948,6 +949,74 @@ __global__ void __launch_bounds__(XV_SL * 32) xf_verify_items_kernel(XfArgs g) {
         atomicAdd(g.stat + 1, 1ULL);
     } else {
         atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(ee));
+    }
+}
+
+// ---- stage A -> stage B work lists, built on the device -----------------------------------------
+// The failing pair-windows of a batch (pf_flag) become an ASCENDING item list and the list of windows that own one,
+// without atomics (the pairing of items in the packed transforms of stage B, and with it every FP32 value, must not
+// depend on scheduling) and without a host pass: count per window (one warp each), one-block scan, ordered write.
+__global__ void __launch_bounds__(256) xf_compact_count_kernel(const unsigned char* flag, int P, int wn, int* cnt) {
+    const int w = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (w >= wn) return;
+    const unsigned char* f = flag + (int64_t)w * P;
+    int c = 0;
+    for (int p = lane; p < P; p += 32) c += f[p] ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+    if (lane == 0) cnt[w] = c;
+}
+// cnt[w] -> off[w] (exclusive prefix), counts[0] = items, counts[1] = windows, wlist[] = band-level indices of those windows
+__global__ void __launch_bounds__(1024) xf_compact_scan_kernel(const int* cnt, int wn, int w0, int* off, int* wlist, int* counts) {
+    __shared__ int wsum[32], wnum[32];
+    __shared__ int base_items, base_wins;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { base_items = 0; base_wins = 0; }
+    __syncthreads();
+    for (int w_ = 0; w_ < wn; w_ += 1024) {
+        const int w = w_ + tid;
+        const int c = w < wn ? cnt[w] : 0, has = c > 0 ? 1 : 0;
+        int s = c, n = has;                      // inclusive scans inside the warp
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int a = __shfl_up_sync(0xffffffffu, s, o), b = __shfl_up_sync(0xffffffffu, n, o);
+            if (lane >= o) { s += a; n += b; }
+        }
+        if (lane == 31) { wsum[warp] = s; wnum[warp] = n; }
+        __syncthreads();
+        if (warp == 0) {
+            int a = wsum[lane], b = wnum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(0xffffffffu, a, o), y = __shfl_up_sync(0xffffffffu, b, o);
+                if (lane >= o) { a += x; b += y; }
+            }
+            wsum[lane] = a; wnum[lane] = b;      // inclusive over warps
+        }
+        __syncthreads();
+        const int pre_s = base_items + (warp ? wsum[warp - 1] : 0) + s - c;
+        const int pre_n = base_wins + (warp ? wnum[warp - 1] : 0) + n - has;
+        if (w < wn) {
+            off[w] = pre_s;
+            if (has) wlist[pre_n] = w0 + w;
+        }
+        __syncthreads();
+        if (tid == 1023) { base_items += wsum[31]; base_wins += wnum[31]; }
+        __syncthreads();
+    }
+    if (tid == 0) { counts[0] = base_items; counts[1] = base_wins; }
+}
+__global__ void __launch_bounds__(256) xf_compact_write_kernel(const unsigned char* flag, int P, int wn, const int* off, int* items) {
+    const int w = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (w >= wn) return;
+    const unsigned char* f = flag + (int64_t)w * P;
+    int pos = off[w];
+    for (int p0 = 0; p0 < P; p0 += 32) {
+        const int p = p0 + lane;
+        const bool hit = p < P && f[p];
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (hit) items[pos + __popc(m & ((1u << lane) - 1u))] = w * P + p;
+        pos += __popc(m);
     }
 }
 
@@ -1143,9 +1212,10 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         NBLS_CHECK(ensure(ctx, ctx->cand, (size_t)wb * P * XF_KC * sizeof(int32_t)));
         NBLS_CHECK(ensure(ctx, ctx->sval, (size_t)wb * P * sizeof(float)));
     }
-    // stage A -> B bookkeeping: [0] failing-pair counter, [1 .. wb*P] failing-pair items, then [wb] window list
+    // stage A -> B bookkeeping: [4] counters, [wb*P] failing-pair items (ascending), [wb] window list, [wb] per-window
+    // counts, [wb] per-window offsets, then [wb*P] bytes of failure flags
     if (pa) {
-        NBLS_CHECK(ensure(ctx, ctx->wfail, ((size_t)wb * P + wb + 4) * sizeof(int)));
+        NBLS_CHECK(ensure(ctx, ctx->wfail, ((size_t)wb * P + 3 * (size_t)wb + 8) * sizeof(int) + (size_t)wb * P + 64));
         NBLS_CUDA(allow_max_dynamic_smem(xf_verify_items_kernel, ctx->smem_optin));
     }
     for (const XfPlan* q : {pl, pa}) {
@@ -1170,7 +1240,9 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
     a.pf_count = (int*)ctx->wfail.p;
     a.pf_list = a.pf_count ? a.pf_count + 4 : nullptr;
     int* dwlist = a.pf_list ? a.pf_list + (size_t)wb * P : nullptr;
-    std::vector<int> hitems, hwin;
+    int* dcnt = dwlist ? dwlist + wb : nullptr;
+    int* doff = dcnt ? dcnt + wb : nullptr;
+    a.pf_flag = doff ? (unsigned char*)(doff + wb + 4) : nullptr;
 
     // undecided arg-maxima are settled by the time-domain kernel (normally an empty list)
     auto settle = [&]() -> int {
@@ -1261,34 +1333,27 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         // stage A: |lag| <= k0 with the shorter transform, plus the proof per pair-window that nothing beyond k0 can win
         a.k0 = std::min(pa->L - N, N - 1); a.lag_max = a.k0;
         a.SP = pa->L / 2 + 1; a.tw = twa;
-        NBLS_CUDA(cudaMemsetAsync(a.pf_count, 0, sizeof(int), ctx->stream));
+        NBLS_CUDA(cudaMemsetAsync(a.pf_flag, 0, (size_t)wn * P, ctx->stream));
         NBLS_CHECK(pass(pa));
-        int nfail = 0;
-        NBLS_CUDA(cudaMemcpyAsync(&nfail, a.pf_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        // stage B work lists on the device; the host only needs the two counts for the launch grids
+        xf_compact_count_kernel<<<(wn + 7) / 8, 256, 0, ctx->stream>>>(a.pf_flag, P, wn, dcnt);
+        NBLS_CUDA(cudaGetLastError());
+        xf_compact_scan_kernel<<<1, 1024, 0, ctx->stream>>>(dcnt, wn, w0, doff, dwlist, a.pf_count);
+        NBLS_CUDA(cudaGetLastError());
+        xf_compact_write_kernel<<<(wn + 7) / 8, 256, 0, ctx->stream>>>(a.pf_flag, P, wn, doff, a.pf_list);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 3;
+        int hcount[2] = {0, 0};
+        NBLS_CUDA(cudaMemcpyAsync(hcount, a.pf_count, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
+        const int nfail = hcount[0], nwin_fail = hcount[1];
         if (nfail == 0) continue;
-        // stage B: the pair-windows without a proof, over all lags.  The list is sorted so that the pairing of items in
-        // the packed transforms (and with it every FP32 value) does not depend on the order the atomics ran in.
-        hitems.resize(nfail);
-        NBLS_CUDA(cudaMemcpyAsync(hitems.data(), a.pf_list, (size_t)nfail * sizeof(int), cudaMemcpyDeviceToHost,
-                                  ctx->stream));
-        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-        std::sort(hitems.begin(), hitems.end());
-        hwin.clear();
-        for (int it : hitems) {
-            const int w = w0 + it / P;
-            if (hwin.empty() || hwin.back() != w) hwin.push_back(w);
-        }
-        n_redo += (int64_t)hwin.size();
+        n_redo += nwin_fail;
         n_redo_pairs += nfail;
-        NBLS_CUDA(cudaMemcpyAsync(a.pf_list, hitems.data(), (size_t)nfail * sizeof(int), cudaMemcpyHostToDevice,
-                                  ctx->stream));
-        NBLS_CUDA(cudaMemcpyAsync(dwlist, hwin.data(), hwin.size() * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
-        NBLS_CUDA(cudaStreamSynchronize(ctx->stream));     // both host lists are pageable and reused
         a.k0 = -1; a.lag_max = lag_full;
         a.SP = SP; a.tw = tw;
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
-        a.wn = (int)hwin.size(); a.wlist = dwlist;
+        a.wn = nwin_fail; a.wlist = dwlist;
         {
             KernelGroupScope ks(ctx, KG_SPECTRA, (double)a.wn * ncp * fft_flop(pl));
             pl->spectra<<<(unsigned)(a.wn * ncp), pl->threads, pl->smem, ctx->stream>>>(a);

@@ -46,6 +46,9 @@ def main():
     ap.add_argument("--key", required=True)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--summary", default=None, help="also write a per-group summary CSV here")
+    ap.add_argument("--only", default=None, help="merge only the groups whose name starts with this prefix into the "
+                    "existing entry (e.g. 'filter_': the filter's state passes are not linear in the record length, "
+                    "so they are captured at full length in a pass of their own)")
     a = ap.parse_args()
     rows = {}
     with open(a.csv, newline="") as f:
@@ -82,10 +85,18 @@ def main():
             allk = json.load(f)
     except Exception:
         allk = {}
-    allk[a.key] = {g: e["bytes"] * a.scale for g, e in groups.items()}
-    allk[a.key + "__meta"] = {"scale": a.scale, "source_csv": os.path.basename(a.csv),
-                              "launches": {g: e["launches"] for g, e in groups.items()},
-                              "ncu_ms_unscaled": {g: e["ms"] for g, e in groups.items()}}
+    if a.only:
+        groups = {g: e for g, e in groups.items() if g.startswith(a.only)}
+        entry, meta = allk.get(a.key, {}), allk.get(a.key + "__meta", {})
+        entry.update({g: e["bytes"] * a.scale for g, e in groups.items()})
+        meta.setdefault("passes", []).append({"only": a.only, "scale": a.scale, "source_csv": os.path.basename(a.csv),
+                                              "ncu_ms_unscaled": {g: e["ms"] for g, e in groups.items()}})
+        allk[a.key], allk[a.key + "__meta"] = entry, meta
+    else:
+        allk[a.key] = {g: e["bytes"] * a.scale for g, e in groups.items()}
+        allk[a.key + "__meta"] = {"scale": a.scale, "source_csv": os.path.basename(a.csv),
+                                  "launches": {g: e["launches"] for g, e in groups.items()},
+                                  "ncu_ms_unscaled": {g: e["ms"] for g, e in groups.items()}}
     with open(out_path, "w") as f:
         json.dump(allk, f, indent=1, sort_keys=True)
     if a.summary:
