@@ -322,6 +322,29 @@ def dist_setup():
     return world, rank, local_rank, dist
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Multi-GPU e2e: run this rank's host threads - and therefore place its pinned buffers (first touch) - on the NUMA
+    node its GPU hangs off, so that eight ranks do not pull their H2D copies through one memory controller.  Returns the
+    node (or None when sysfs does not say)."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local_rank)
+        dev = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{dev}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            cpus = set()
+            for part in f.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        os.sched_setaffinity(0, cpus & os.sched_getaffinity(0) or cpus)
+        return node
+    except Exception:
+        return None
+
+
 def xcorr_method(args):
     from narrow_band_least_squares_b200 import _capi
     return {"auto": _capi.XCORR_AUTO, "direct": _capi.XCORR_DIRECT, "fft": _capi.XCORR_FFT, "fft64": _capi.XCORR_FFT,
@@ -413,6 +436,7 @@ def run_single(args):
     from narrow_band_least_squares_b200.sharding import PackedGather, all_shards, filter_halo
 
     world, rank, local_rank, dist = dist_setup()
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     j = workload(args)
     method = xcorr_method(args)
     fs, nchan, nb = j["fs"], j["nchans"], j["nbands"]
@@ -576,6 +600,7 @@ def run_single(args):
                "ms_per_step_wall": e_wall / args.steps, "ms_record_latency_device": e_ms / args.steps,
                "records_in_flight": nfl,
                "h2d_gbs_per_rank": (x_host.nbytes / 1e9) / (h_ms / args.steps * 1e-3) if h_ms > 0 else None,
+               "host_numa_node_rank0": numa,
                "note": ("two records in flight on two contexts: e2e can exceed `value` because the tail of one record "
                         "(low-occupancy last waves, D2H) overlaps the head of the next; one record alone takes "
                         "ms_record_latency_device") if nfl > 1 else None}

@@ -69,11 +69,14 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
 }
 
-// One warp, 32 consecutive chunks of one (band, channel).  EDGE = false is the interior fast path: every chunk of
-// the warp is whole and no sample lies in the taper zones, so loads and stores carry no bounds or taper logic.
-template <int S, bool REV, bool EDGE, bool STATE_ONLY, bool FUSED>
+// One warp, 32 consecutive chunks of one (band, channel).  MODE 0 is the interior fast path: every chunk of the warp is
+// whole and no sample lies in the taper zones, so loads and stores carry no bounds or taper logic.  MODE 1: whole chunks
+// inside a taper zone - no bounds logic, the stores multiply by the ramp (the first / last 1 % of a LONG record is many
+// chunks: on the edge ranks of a time-sharded run it used to cost 9 ms of a 29 ms filter).  MODE 2: ragged record end.
+template <int S, bool REV, int MODE, bool STATE_ONLY, bool FUSED>
 __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, int band, int chan, int64_t chunk0,
                                             int lane) {
+    constexpr bool EDGE = MODE == 2;
     const int ntiles = a.L / FT_TILE;
     int first = 0;
     if (a.proc_tiles) first = ntiles - min(ntiles, a.proc_tiles[band]);
@@ -181,7 +184,15 @@ __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, i
             for (int q = 0; q < FT_REQS; ++q) {
                 double2 d = *reinterpret_cast<const double2*>(srow + q * FT_ROWS_PER_REQ * FT_ROW);
                 const int64_t t = t0 + q * slot_stride;
-                if constexpr (!EDGE) {
+                if constexpr (MODE == 0) {
+                    *reinterpret_cast<double2*>(out + t) = d;
+                } else if constexpr (MODE == 1) {
+                    const int64_t g = a.g0 + t;
+                    const int64_t dn = a.G - a.taper_len;
+                    if (g < a.taper_len) d.x = __dmul_rn(d.x, a.taper_up[g]);
+                    if (g + 1 < a.taper_len) d.y = __dmul_rn(d.y, a.taper_up[g + 1]);
+                    if (g >= dn) d.x = __dmul_rn(d.x, a.taper_down[g - dn]);
+                    if (g + 1 >= dn) d.y = __dmul_rn(d.y, a.taper_down[g + 1 - dn]);
                     *reinterpret_cast<double2*>(out + t) = d;
                 } else {
                     const int64_t k = chunk0 + row0 + q * FT_ROWS_PER_REQ;
@@ -222,17 +233,18 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
     // interior warp: its 32 chunks are whole (none is the record's ragged last chunk) and, when a taper is applied by
     // this launch, none of its samples lies in the first / last taper_len samples of the global record
     const int64_t s_lo = chunk0 * a.L, s_hi = (chunk0 + 32) * a.L;          // local sample range [s_lo, s_hi)
-    bool edge = s_hi > a.T;
-    if (a.out && a.taper_len > 0)
-        edge = edge || (a.g0 + s_lo < a.taper_len) || (a.g0 + s_hi > a.G - a.taper_len);
+    const bool edge = s_hi > a.T;
+    const bool tapered = a.out && a.taper_len > 0 &&
+                         ((a.g0 + s_lo < a.taper_len) || (a.g0 + s_hi > a.G - a.taper_len));
     if (!a.out) {     // phase 1: chunk end states only
-        if (edge) biquad_warp<S, REV, true, true, true>(a, ring, band, chan, chunk0, lane);
-        else biquad_warp<S, REV, false, true, true>(a, ring, band, chan, chunk0, lane);
+        if (edge) biquad_warp<S, REV, 2, true, true>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, 0, true, true>(a, ring, band, chan, chunk0, lane);
     } else if (a.nchunks > 1) {
-        if (edge) biquad_warp<S, REV, true, false, true>(a, ring, band, chan, chunk0, lane);
-        else biquad_warp<S, REV, false, false, true>(a, ring, band, chan, chunk0, lane);
+        if (edge) biquad_warp<S, REV, 2, false, true>(a, ring, band, chan, chunk0, lane);
+        else if (tapered) biquad_warp<S, REV, 1, false, true>(a, ring, band, chan, chunk0, lane);
+        else biquad_warp<S, REV, 0, false, true>(a, ring, band, chan, chunk0, lane);
     } else {
-        biquad_warp<S, REV, true, false, false>(a, ring, band, chan, chunk0, lane);
+        biquad_warp<S, REV, 2, false, false>(a, ring, band, chan, chunk0, lane);
     }
 }
 
@@ -439,15 +451,22 @@ __global__ void carry_kernel(double* state, const double* ML, int B, int C, int 
 }
 
 typedef void (*state_fn)(FilterArgs);
+// only the combinations pick_state() can select are instantiated: S * NBW <= 10 recurrence states per lane (more would
+// not fit in 128 registers: those variants used to be compiled, spilling kilobytes, and never run)
+template <int S, int NBW>
+static state_fn state_kernel_or_null() {
+    if constexpr (S * NBW <= 10) return biquad_state_shared_kernel<S, NBW>;
+    else return nullptr;
+}
 template <int S>
 static state_fn pick_state_nbw(int nbw) {
     switch (nbw) {
-        case 1: return biquad_state_shared_kernel<S, 1>;
-        case 2: return biquad_state_shared_kernel<S, 2>;
-        case 3: return biquad_state_shared_kernel<S, 3>;
-        case 4: return biquad_state_shared_kernel<S, 4>;
-        case 5: return biquad_state_shared_kernel<S, 5>;
-        case 6: return biquad_state_shared_kernel<S, 6>;
+        case 1: return state_kernel_or_null<S, 1>();
+        case 2: return state_kernel_or_null<S, 2>();
+        case 3: return state_kernel_or_null<S, 3>();
+        case 4: return state_kernel_or_null<S, 4>();
+        case 5: return state_kernel_or_null<S, 5>();
+        case 6: return state_kernel_or_null<S, 6>();
         default: return nullptr;
     }
 }
