@@ -69,8 +69,11 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and parity legs")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-profile", action="store_true", help="skip the profiled step (kernel_groups)")
-    ap.add_argument("--e2e-in-flight", type=int, default=2,
-                    help="records in flight in the e2e leg (own context each; 1 = strictly one after the other)")
+    ap.add_argument("--opt", action="append", default=[], metavar="KEY=VALUE",
+                    help="libnbls context option by number (include/nbls.h NBLS_OPT_*), e.g. --opt 7=4")
+    ap.add_argument("--e2e-in-flight", type=int, default=3,
+                    help="records in flight in the e2e leg (own context and workspace each, capped by what fits in HBM; "
+                         "1 = strictly one after the other)")
     return ap.parse_args()
 
 
@@ -453,6 +456,8 @@ def run_single(args):
     eng = Engine(local_rank)
     if args.single_stage:
         eng.set_option(_capi.OPT_TWO_STAGE, 0)
+    for kv in args.opt:
+        eng.set_option(int(kv.split("=")[0]), int(kv.split("=")[1]))
     x_dev, x_host, rij = segment_record(j, args, shard.seg_lo, shard.seg_hi, ld, local_rank, world)
     plan = shard.plan(nchan, fs, sos, j["filter_type"] == "butter", win_len, win_hop, rij, alpha=j["alpha"],
                       max_lag=args.max_lag, method=method)
@@ -535,11 +540,18 @@ def run_single(args):
 
     e2e = None
     if not args.no_e2e:
-        nfl = max(1, min(args.e2e_in_flight, args.steps))
+        # every context in flight holds its own workspace (filtered bands of all B bands + record + ~8 GB of cross-
+        # correlation buffers): as many as fit in 80 % of the HBM, at most --e2e-in-flight
+        import torch
+        per_ctx = 8.0 * nchan * ld * (nb + 1) + 8e9
+        fit = int(0.8 * torch.cuda.get_device_properties(local_rank).total_memory / per_ctx)
+        nfl = max(1, min(args.e2e_in_flight, args.steps, fit))
         engs = [eng] + [Engine(local_rank) for _ in range(nfl - 1)]
-        if args.single_stage:
-            for e_ in engs[1:]:
+        for e_ in engs[1:]:
+            if args.single_stage:
                 e_.set_option(_capi.OPT_TWO_STAGE, 0)
+            for kv in args.opt:
+                e_.set_option(int(kv.split("=")[0]), int(kv.split("=")[1]))
         ress = [res] + [Results(plan, pinned=True, want_cmax=False) for _ in range(nfl - 1)]
         for e_, r_ in zip(engs, ress):
             e_.run(plan, x_host, r_)                          # one warm-up each (buffers grow once)
@@ -601,9 +613,9 @@ def run_single(args):
                "records_in_flight": nfl,
                "h2d_gbs_per_rank": (x_host.nbytes / 1e9) / (h_ms / args.steps * 1e-3) if h_ms > 0 else None,
                "host_numa_node_rank0": numa,
-               "note": ("two records in flight on two contexts: e2e can exceed `value` because the tail of one record "
-                        "(low-occupancy last waves, D2H) overlaps the head of the next; one record alone takes "
-                        "ms_record_latency_device") if nfl > 1 else None}
+               "note": (f"{nfl} records in flight, one context each: the H2D copy, the D2H copies and the host-side waits of "
+                        "one record overlap the kernels of the others; one record alone spends ms_record_latency_device "
+                        "in flight") if nfl > 1 else None}
         for e_ in engs[1:]:
             e_.close()
 
@@ -868,8 +880,9 @@ def config_block(j, world, args, extra=None):
     c = {"workload": wl, "sharding": shard, "l2": "inputs larger than L2 (record and filtered bands are GB-sized)",
          "xcorr_method": args.method + (" (single-stage)" if args.single_stage else ""), "max_lag": args.max_lag,
          "record": "incoherent noise (plane wave 30 dB down)" if args.noise_only else "synthetic plane wave + noise, every 10th minute noise-only",
-         "e2e": (f"{max(1, min(args.e2e_in_flight, args.steps))} record(s) in flight, one context each; every step copies its "
-                 "input from pinned host memory and its results back inside the timed region")}
+         "e2e": (f"up to {max(1, min(args.e2e_in_flight, args.steps))} record(s) in flight (see e2e.records_in_flight), one "
+                 "context each; every step copies its input from pinned host memory and its results back inside the "
+                 "timed region")}
     if extra:
         c.update(extra)
     return c

@@ -47,8 +47,9 @@ struct FilterArgs {
     int64_t out_row, out_band;
     const double* coef;        // [B][S][5] b0 b1 b2 a1 a2
     const int* proc_tiles;     // [B] tiles per chunk to run in phase 1 (from the chunk's end)
-    const double* state_in;    // [B][C][nchunks][2S] or nullptr (zero)
-    double* state_out;         // same layout or nullptr
+    const double* state_in;    // [B][C][sin_n][2S] or nullptr (zero); chunk k starts from entry sin_mul * k + sin_off
+    double* state_out;         // [B][C][nchunks][2S] or nullptr
+    int sin_n, sin_mul, sin_off;   // the state pass may run on SUB-chunks (forward pass): sin_n = its chunk count
     int B, C;
     int64_t T;
     int L, nchunks;
@@ -94,8 +95,9 @@ __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, i
     const bool valid = !EDGE || mychunk < a.nchunks;
     const int64_t sidx = (((int64_t)band * a.C + chan) * a.nchunks + mychunk) * (2 * S);
     if (a.state_in && valid) {
+        const int64_t rin = (((int64_t)band * a.C + chan) * a.sin_n + mychunk * a.sin_mul + a.sin_off) * (2 * S);
 #pragma unroll
-        for (int s = 0; s < S; ++s) { z0[s] = a.state_in[sidx + 2 * s]; z1[s] = a.state_in[sidx + 2 * s + 1]; }
+        for (int s = 0; s < S; ++s) { z0[s] = a.state_in[rin + 2 * s]; z1[s] = a.state_in[rin + 2 * s + 1]; }
     }
 
     // the copy this lane performs for each of its slots of a tile: row = slot*ROWS_PER_REQ + lane/SEGS
@@ -256,7 +258,8 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
 // reach the same samples milliseconds apart, far beyond the residency of a line in L2).  Needs proc_tiles to be
 // non-increasing over the band index (bands ordered by rising frequency), so that the active bands of a warp are a
 // prefix of its list; the host checks that.  Same arithmetic per band as biquad_warp<.., STATE_ONLY>.
-constexpr int FS_WARPS = 4;
+// FSW = warps per block (template parameter): 4, or 8 when more than 12 bands share a tile (then a warp carries at most
+// three bands and takes them in ONE sweep per tile instead of two)
 // bands [Q0, Q0 + NA) of the warp's list over one tile row
 template <int S, int NBW, int Q0, int NA>
 __device__ __forceinline__ void state_tile(const double* row, const double (*cf)[5], double (&z0)[NBW][S],
@@ -287,8 +290,8 @@ __device__ __forceinline__ void state_tile(const double* row, const double (*cf)
     }
 }
 
-template <int S, int NBW>
-__global__ void __launch_bounds__(FS_WARPS * 32, 4) biquad_state_shared_kernel(FilterArgs a) {
+template <int S, int NBW, int FS_WARPS>
+__global__ void __launch_bounds__(FS_WARPS * 32, 512 / (FS_WARPS * 32)) biquad_state_shared_kernel(FilterArgs a) {
     extern __shared__ __align__(16) double smem[];
     __shared__ double coef_sh[FS_WARPS][NBW * S][5];
     __shared__ int first_sh[FS_WARPS][NBW];
@@ -453,32 +456,36 @@ __global__ void carry_kernel(double* state, const double* ML, int B, int C, int 
 typedef void (*state_fn)(FilterArgs);
 // only the combinations pick_state() can select are instantiated: S * NBW <= 10 recurrence states per lane (more would
 // not fit in 128 registers: those variants used to be compiled, spilling kilobytes, and never run)
-template <int S, int NBW>
+template <int S, int NBW, int FSW>
 static state_fn state_kernel_or_null() {
-    if constexpr (S * NBW <= 10) return biquad_state_shared_kernel<S, NBW>;
+    if constexpr (S * NBW <= 10) return biquad_state_shared_kernel<S, NBW, FSW>;
     else return nullptr;
 }
-template <int S>
+template <int S, int FSW>
 static state_fn pick_state_nbw(int nbw) {
     switch (nbw) {
-        case 1: return state_kernel_or_null<S, 1>();
-        case 2: return state_kernel_or_null<S, 2>();
-        case 3: return state_kernel_or_null<S, 3>();
-        case 4: return state_kernel_or_null<S, 4>();
-        case 5: return state_kernel_or_null<S, 5>();
-        case 6: return state_kernel_or_null<S, 6>();
+        case 1: return state_kernel_or_null<S, 1, FSW>();
+        case 2: return state_kernel_or_null<S, 2, FSW>();
+        case 3: return state_kernel_or_null<S, 3, FSW>();
+        case 4: return state_kernel_or_null<S, 4, FSW>();
+        case 5: return state_kernel_or_null<S, 5, FSW>();
+        case 6: return state_kernel_or_null<S, 6, FSW>();
         default: return nullptr;
     }
 }
-static state_fn pick_state(int S, int nbw) {
+template <int FSW>
+static state_fn pick_state_w(int S, int nbw) {
     if (S * nbw > 10) return nullptr;      // more states than fit in 128 registers: the per-band kernel serves
     switch (S) {
-        case 1: return pick_state_nbw<1>(nbw);
-        case 2: return pick_state_nbw<2>(nbw);
-        case 3: return pick_state_nbw<3>(nbw);
-        case 4: return pick_state_nbw<4>(nbw);
+        case 1: return pick_state_nbw<1, FSW>(nbw);
+        case 2: return pick_state_nbw<2, FSW>(nbw);
+        case 3: return pick_state_nbw<3, FSW>(nbw);
+        case 4: return pick_state_nbw<4, FSW>(nbw);
         default: return nullptr;
     }
+}
+static state_fn pick_state(int S, int per_block, int fsw) {
+    return fsw == 8 ? pick_state_w<8>(S, (per_block + 7) / 8) : pick_state_w<4>(S, (per_block + 3) / 4);
 }
 
 typedef void (*carry_fn)(double*, const double*, int, int, int, int);
@@ -583,11 +590,18 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
 
     // chunking
     int64_t L = d->chunk_len;
+    // The forward state pass (phase 1) is bound by the LATENCY of its dependent FP64 recurrence, one chunk per lane: it runs
+    // on sub-chunks of L / sub samples (sub x the lanes, chains sub x shorter; the carry then walks sub x the states and
+    // phase 3 picks every sub-th one).  The backward state pass is bandwidth-bound and keeps whole chunks.
+    int sub = (int)ctx->opt[NBLS_OPT_FILTER_P1_SUB];
+    if (sub != 1 && sub != 2 && sub != 4 && sub != 8) sub = 4;
+    if (d->exact_scan) sub = 1;
     if (L <= 0) {
         const double lanes = (double)ctx->opt[NBLS_OPT_FILTER_LANES];
-        L = round_up((int64_t)((double)T * B * C / lanes), FT_TILE);
+        L = round_up((int64_t)((double)T * B * C / lanes), FT_TILE * sub);
         L = std::max<int64_t>(256, std::min<int64_t>(65536, L));
     }
+    while (sub > 1 && (L % (FT_TILE * sub) != 0 || L / sub < 4 * FT_TILE)) sub >>= 1;
     NBLS_REQUIRE(L % FT_TILE == 0 && L >= FT_TILE, "nbls_filter: chunk_len must be a positive multiple of %d", FT_TILE);
     L = std::min<int64_t>(L, round_up(T, FT_TILE));
     const int64_t nchunks64 = (T + L - 1) / L;
@@ -595,11 +609,14 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     const int nchunks = (int)nchunks64;
     const int ntiles = (int)(L / FT_TILE);
     const int S2 = 2 * S;
+    if (nchunks <= 1) sub = 1;
+    const int64_t L1 = L / sub;                                  // sub-chunk length of the forward state pass
+    const int nchunks1 = (int)((T + L1 - 1) / L1), ntiles1 = (int)(L1 / FT_TILE);
 
     // host-side tables: coefficients, A^L, phase-1 lengths
     const size_t n_coef = (size_t)B * S * 5, n_ml = (size_t)B * S2 * S2;
-    std::vector<double> hbuf(n_coef + n_ml);
-    std::vector<int> hproc(B);
+    std::vector<double> hbuf(n_coef + 2 * n_ml);                 // coefficients, A^L (backward carry), A^L1 (forward carry)
+    std::vector<int> hproc(2 * B);                               // phase-1 tiles per chunk: backward [B], forward [B]
     for (int b = 0; b < B; ++b) {
         const double* sb = d->sos + (size_t)b * S * 6;
         for (int s = 0; s < S; ++s) {
@@ -610,23 +627,45 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         std::vector<double> ml;
         transition_power(sb, S, L, ml);
         memcpy(&hbuf[n_coef + (size_t)b * S2 * S2], ml.data(), sizeof(double) * S2 * S2);
-        int pt = ntiles;
+        transition_power(sb, S, L1, ml);
+        memcpy(&hbuf[n_coef + n_ml + (size_t)b * S2 * S2], ml.data(), sizeof(double) * S2 * S2);
+        int pt = ntiles, pt1 = ntiles1;
         if (!d->exact_scan) {
             const double r = max_pole_radius(sb, S);
             if (r > 0.0 && r < 1.0) {
-                const double K = ceil(64.0 * M_LN2 / -log(r));
+                // K from the spectral radius, then grown until the transition matrix itself has decayed: the cascade of a
+                // narrow band-pass is strongly non-normal (its poles cluster), so ||A^K|| can exceed r^K by orders of magnitude
+                double K = ceil(64.0 * M_LN2 / -log(r));
+                const double target = ldexp(1.0, -64);
+                for (int grow = 0; grow < 64 && K < (double)L; ++grow) {
+                    std::vector<double> ak;
+                    transition_power(sb, S, (int64_t)K, ak);
+                    double nrm = 0.0;
+                    for (int i = 0; i < S2; ++i) {
+                        double row = 0.0;
+                        for (int jn = 0; jn < S2; ++jn) row += fabs(ak[i * S2 + jn]);
+                        nrm = std::max(nrm, row);
+                    }
+                    if (nrm <= target) break;
+                    K = ceil(K + std::max(32.0, log(nrm / target) / -log(r)));
+                }
                 if (K < (double)L) pt = (int)std::min<double>(ntiles, ceil(K / FT_TILE));
+                if (K < (double)L1) pt1 = (int)std::min<double>(ntiles1, ceil(K / FT_TILE));
             } else if (r == 0.0) {
                 pt = std::min(ntiles, 2 * S / FT_TILE + 1);   // FIR: state forgets after 2 samples/section
+                pt1 = std::min(ntiles1, 2 * S / FT_TILE + 1);
             }
         }
         hproc[b] = pt;
+        hproc[B + b] = pt1;
     }
-    const size_t coef_bytes = hbuf.size() * sizeof(double) + round_up(B * sizeof(int), 16);
+    const size_t coef_bytes = hbuf.size() * sizeof(double) + round_up(2 * B * sizeof(int), 16);
     NBLS_CHECK(ensure(ctx, ctx->coef, coef_bytes));
     double* dcoef = (double*)ctx->coef.p;
     double* dml = dcoef + n_coef;
-    int* dproc = (int*)(dml + n_ml);
+    double* dml1 = dml + n_ml;
+    int* dproc = (int*)(dml1 + n_ml);
+    int* dproc1 = dproc + B;
     // The device copies of the tables are kept between calls: a caller that repeats a job (a queue of records with one
     // band plan) pays the two uploads and their synchronisations - a few hundred microseconds of idle GPU - only once.
     std::vector<unsigned char> key(hbuf.size() * sizeof(double) + hproc.size() * sizeof(int) + 2 * d->taper_len * sizeof(double));
@@ -645,7 +684,7 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     if (d->taper_len > 0) NBLS_CHECK(ensure(ctx, ctx->taper, 2 * d->taper_len * sizeof(double)));
     if (!cached || (d->taper_len > 0 && ctx->filter_key_taper != ctx->taper.p)) {
         NBLS_CUDA(cudaMemcpyAsync(dcoef, hbuf.data(), hbuf.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
-        NBLS_CUDA(cudaMemcpyAsync(dproc, hproc.data(), B * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+        NBLS_CUDA(cudaMemcpyAsync(dproc, hproc.data(), 2 * B * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
         if (d->taper_len > 0) {
             double* tp = (double*)ctx->taper.p;
             NBLS_CUDA(cudaMemcpyAsync(tp, d->taper_up, d->taper_len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
@@ -664,7 +703,7 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     }
     double* dstate = nullptr;
     if (nchunks > 1) {
-        NBLS_CHECK(ensure(ctx, ctx->state, (size_t)B * C * nchunks * S2 * sizeof(double)));
+        NBLS_CHECK(ensure(ctx, ctx->state, (size_t)B * C * nchunks1 * S2 * sizeof(double)));
         dstate = (double*)ctx->state.p;
     }
 
@@ -680,44 +719,58 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     // The bands are dealt to `nsplit` blocks per (32 chunks, channel) so that a warp carries at most three of them: a lane's
     // recurrences are serial over the chunk, and the longest (lowest band, whole chunk) sets the kernel time.
     state_fn shared_p1 = nullptr;
-    int nsplit = 1;
+    int nsplit = 1, p1_warps = 4;
     {
         bool mono = true;
-        for (int b = 1; b < B; ++b) mono = mono && hproc[b] <= hproc[b - 1];
+        for (int b = 1; b < B; ++b) mono = mono && hproc[B + b] <= hproc[B + b - 1];
         nsplit = (int)std::max<int64_t>(1, ctx->opt[NBLS_OPT_FILTER_SPLIT]);
         const int per_block = (B + nsplit - 1) / nsplit;
         if (mono && nchunks > 1 && ctx->opt[NBLS_OPT_FILTER_SHARED_P1])
-            shared_p1 = pick_state(S, (per_block + FS_WARPS - 1) / FS_WARPS);
+        {
+            // warps per block: 8 when 4 would leave a warp with more than three bands (two sweeps per tile), else 4
+            p1_warps = (int)ctx->opt[NBLS_OPT_FILTER_P1_WARPS];
+            if (p1_warps != 4 && p1_warps != 8) p1_warps = ((per_block + 3) / 4 > 3) ? 8 : 4;
+            shared_p1 = pick_state(S, per_block, p1_warps);
+            if (!shared_p1 && p1_warps == 4) { p1_warps = 8; shared_p1 = pick_state(S, per_block, 8); }
+        }
     }
     auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
         chunk_fn fn = pick(S, rev);
         FilterArgs a;
         memset(&a, 0, sizeof(a));
         a.in = in; a.in_row = in_row; a.in_band = in_band;
-        a.coef = dcoef; a.B = B; a.C = C; a.T = T; a.L = (int)L; a.nchunks = nchunks;
+        a.coef = dcoef; a.B = B; a.C = C; a.T = T;
+        // the state pass of the forward direction runs on sub-chunks (see above), the backward one on whole chunks
+        const int psub = rev ? 1 : sub;
+        const int pn = rev ? nchunks : nchunks1;
         if (nchunks > 1) {
-            a.out = nullptr; a.proc_tiles = dproc; a.state_in = nullptr; a.state_out = dstate;
+            a.L = (int)(rev ? L : L1); a.nchunks = pn;
+            a.out = nullptr; a.proc_tiles = rev ? dproc : dproc1; a.state_in = nullptr; a.state_out = dstate;
+            const dim3 grid1(grid.x, (pn + 31) / 32, C);
+            NBLS_REQUIRE(grid1.y <= 65535, "nbls_filter: chunk grid too large (raise chunk_len)");
             {
                 KernelGroupScope ks(ctx, rev ? KG_FILTER_P1B : KG_FILTER_P1F, 0.0);   // state passes: no algorithmic bytes
                 if (!rev && in_band == 0 && shared_p1) {
                     // every band reads the same record: one read of each tile for all bands
                     const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
                     a.nsplit = nsplit;
-                    shared_p1<<<dim3(grid.y, C, nsplit), FS_WARPS * 32, smem1, ctx->stream>>>(a);
+                    shared_p1<<<dim3(grid1.y, C, nsplit), p1_warps * 32, smem1, ctx->stream>>>(a);
                 } else {
-                    fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+                    fn<<<grid1, FT_WARPS * 32, smem, ctx->stream>>>(a);
                 }
             }
             NBLS_CUDA(cudaGetLastError());
             {
                 KernelGroupScope ks(ctx, KG_FILTER_CARRY, 0.0);
-                pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, dml, B, C, nchunks, rev ? 1 : 0);
+                pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, rev ? dml : dml1, B, C, pn, rev ? 1 : 0);
             }
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 2;
         }
+        a.L = (int)L; a.nchunks = nchunks;
         a.out = y; a.out_row = ldy; a.out_band = ystride_band;
-        a.proc_tiles = nullptr; a.state_in = dstate; a.state_out = nullptr;
+        a.proc_tiles = nullptr; a.state_in = nchunks > 1 ? dstate : nullptr; a.state_out = nullptr;
+        a.sin_n = pn; a.sin_mul = psub; a.sin_off = 0;
         if (taper) {
             a.taper_up = dup; a.taper_down = ddown; a.taper_len = d->taper_len; a.g0 = d->global_t0;
             a.G = d->global_npts > 0 ? d->global_npts : T;
