@@ -590,11 +590,12 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
 
     // chunking
     int64_t L = d->chunk_len;
-    // The forward state pass (phase 1) is bound by the LATENCY of its dependent FP64 recurrence, one chunk per lane: it runs
-    // on sub-chunks of L / sub samples (sub x the lanes, chains sub x shorter; the carry then walks sub x the states and
-    // phase 3 picks every sub-th one).  The backward state pass is bandwidth-bound and keeps whole chunks.
+    // The forward state pass (phase 1) can run on sub-chunks of L / sub samples (sub x the lanes, recurrence chains sub x
+    // shorter; the carry then walks sub x the states and phase 3 picks every sub-th one).  Measured on c3/24 h (B200):
+    // sub = 1 / 2 / 4 / 8 -> 2.96 / 3.07 / 3.61 / 3.71 ms: the pass is bound by its FP64 work, which grows with sub (every
+    // sub-chunk reruns its K_b tail), not by the latency of the chains - the default stays 1; NBLS_OPT_FILTER_P1_SUB selects.
     int sub = (int)ctx->opt[NBLS_OPT_FILTER_P1_SUB];
-    if (sub != 1 && sub != 2 && sub != 4 && sub != 8) sub = 4;
+    if (sub != 1 && sub != 2 && sub != 4 && sub != 8) sub = 1;
     if (d->exact_scan) sub = 1;
     if (L <= 0) {
         const double lanes = (double)ctx->opt[NBLS_OPT_FILTER_LANES];

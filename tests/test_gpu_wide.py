@@ -304,7 +304,12 @@ def test_filter_high_order_narrow_band(eng, order):
         arr[:, x.shape[1] - wlen:] *= down
     rms = np.sqrt(np.mean(np.asarray(exact, dtype=np.float64) ** 2, axis=1, keepdims=True))
     err_scipy = float(np.max(np.abs(f64 - exact) / rms))
-    for kw in (dict(chunk_len=8192), dict(chunk_len=65536), dict(chunk_len=8192, exact_scan=True), dict()):
-        out = eng.filter_bands(x, fs, [sos], zerophase=True, **kw)[0]
-        err = float(np.max(np.abs(out - exact) / rms))
-        assert err <= max(3.0 * err_scipy, 3e-12), (order, kw, err, err_scipy)
+    try:
+        for sub in (1, 4):          # forward state pass on whole chunks (default) and on sub-chunks (NBLS_OPT_FILTER_P1_SUB)
+            eng.set_option(_capi.OPT_FILTER_P1_SUB, sub)
+            for kw in (dict(chunk_len=8192), dict(chunk_len=65536), dict(chunk_len=8192, exact_scan=True), dict()):
+                out = eng.filter_bands(x, fs, [sos], zerophase=True, **kw)[0]
+                err = float(np.max(np.abs(out - exact) / rms))
+                assert err <= max(3.0 * err_scipy, 3e-12), (order, sub, kw, err, err_scipy)
+    finally:
+        eng.set_option(_capi.OPT_FILTER_P1_SUB, 1)
