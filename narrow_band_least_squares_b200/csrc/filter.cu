@@ -669,18 +669,17 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     int* dproc1 = dproc + B;
     // The device copies of the tables are kept between calls: a caller that repeats a job (a queue of records with one
     // band plan) pays the two uploads and their synchronisations - a few hundred microseconds of idle GPU - only once.
-    std::vector<unsigned char> key(hbuf.size() * sizeof(double) + hproc.size() * sizeof(int) + 2 * d->taper_len * sizeof(double));
-    {
-        unsigned char* kp = key.data();
-        memcpy(kp, hbuf.data(), hbuf.size() * sizeof(double)); kp += hbuf.size() * sizeof(double);
-        memcpy(kp, hproc.data(), hproc.size() * sizeof(int)); kp += hproc.size() * sizeof(int);
-        if (d->taper_len > 0) {
-            memcpy(kp, d->taper_up, d->taper_len * sizeof(double)); kp += d->taper_len * sizeof(double);
-            memcpy(kp, d->taper_down, d->taper_len * sizeof(double));
-        }
-    }
-    const bool cached = ctx->filter_key == key && ctx->filter_key_coef == ctx->coef.p &&
-                        (d->taper_len == 0 || ctx->filter_key_taper == ctx->taper.p);
+    // (compared segment by segment against the kept host image: no allocation and one memcmp pass - the taper ramps of a
+    // time-sharded multi-day record are megabytes)
+    const size_t k_coef = hbuf.size() * sizeof(double), k_proc = hproc.size() * sizeof(int);
+    const size_t k_tap = (size_t)d->taper_len * sizeof(double);
+    const std::vector<unsigned char>& fk = ctx->filter_key;
+    bool cached = fk.size() == k_coef + k_proc + 2 * k_tap && ctx->filter_key_coef == ctx->coef.p &&
+                  (d->taper_len == 0 || ctx->filter_key_taper == ctx->taper.p);
+    cached = cached && memcmp(fk.data(), hbuf.data(), k_coef) == 0 && memcmp(fk.data() + k_coef, hproc.data(), k_proc) == 0;
+    if (cached && d->taper_len > 0)
+        cached = memcmp(fk.data() + k_coef + k_proc, d->taper_up, k_tap) == 0 &&
+                 memcmp(fk.data() + k_coef + k_proc + k_tap, d->taper_down, k_tap) == 0;
     const double *dup = nullptr, *ddown = nullptr;
     if (d->taper_len > 0) NBLS_CHECK(ensure(ctx, ctx->taper, 2 * d->taper_len * sizeof(double)));
     if (!cached || (d->taper_len > 0 && ctx->filter_key_taper != ctx->taper.p)) {
@@ -694,7 +693,14 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         }
         // pageable sources: wait until the copies have left the host buffers
         NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
-        ctx->filter_key.swap(key);
+        std::vector<unsigned char>& key = ctx->filter_key;
+        key.resize(k_coef + k_proc + 2 * k_tap);
+        memcpy(key.data(), hbuf.data(), k_coef);
+        memcpy(key.data() + k_coef, hproc.data(), k_proc);
+        if (d->taper_len > 0) {
+            memcpy(key.data() + k_coef + k_proc, d->taper_up, k_tap);
+            memcpy(key.data() + k_coef + k_proc + k_tap, d->taper_down, k_tap);
+        }
         ctx->filter_key_coef = ctx->coef.p;
         ctx->filter_key_taper = d->taper_len > 0 ? ctx->taper.p : nullptr;
     }

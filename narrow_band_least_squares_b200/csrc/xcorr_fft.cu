@@ -165,7 +165,10 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
     const double* xa = g.y + (int64_t)ca * g.ldy + t0;
     const double* xb = g.y + (int64_t)(has_b ? cb : ca) * g.ldy + t0;
 
-    // energies (same accumulation as the time-domain kernel: strided fma, then tree)
+    // ONE pass over the window: energies (same accumulation as the time-domain kernel: strided fma, then tree) and the
+    // samples, rounded to the transform's precision but not yet scaled, into the transform array in natural order.  (A
+    // first pass for the energies and a second, strided one for the transform inputs left the CTA waiting twice for
+    // the same DRAM-resident samples.)  The unit-energy scale is applied when pass 1 picks its inputs up.
     double ea = 0.0, eb = 0.0;
     if (g.k0 >= 0) {
         // stage A of the two-stage search: also the head (n < N-k0-1) and tail (n > k0) energies of both channels
@@ -179,6 +182,7 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
             eb = fma(vb, vb, eb);
             if (n < nh) { ha += qa; hb += qb; }
             if (n > nt) { ta += qa; tb += qb; }
+            sm[S::pad(n)] = mk2((F)va, (F)vb);
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
@@ -197,8 +201,10 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
             const double va = xa[n], vb = xb[n];
             ea = fma(va, va, ea);
             eb = fma(vb, vb, eb);
+            sm[S::pad(n)] = mk2((F)va, (F)vb);
         }
     }
+    for (int n = g.N + tid; n < S::L; n += T) sm[S::pad(n)] = mk2((F)0, (F)0);      // zero padding of the window
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         ea += __shfl_xor_sync(0xffffffffu, ea, o);
@@ -217,16 +223,18 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
         rs_sh[1] = (Eb > 0.0 && isfinite(Eb)) ? 1.0 / sqrt(Eb) : 0.0;
     }
     __syncthreads();
-    const double rsa = rs_sh[0], rsb = rs_sh[1];
+    const F rsa = (F)rs_sh[0], rsb = (F)rs_sh[1];
 
-    // pass 1: inputs conj(z)[n] = (x_a[n], -x_b[n]) * scale, zero beyond the window (scaled in FP64, then
-    // rounded to the transform's precision)
+    // pass 1 in place: inputs conj(z)[n] = (x_a[n], -x_b[n]) * scale from the array (pad(f0 + M1 k) = pad(f0) + k (M1 + R2));
+    // a thread reads and writes the same R1 slots
     for (int f0 = tid; f0 < S::M1; f0 += T) {
         V z[S::R1];
+        const V* base = sm + S::pad(f0);
 #pragma unroll
         for (int k = 0; k < S::R1; ++k) {
-            const int n = f0 + S::M1 * k;
-            z[k] = n < g.N ? mk2((F)(xa[n] * rsa), (F)(-(xb[n] * rsb))) : mk2((F)0, (F)0);
+            const V v = base[k * (S::M1 + S::R2)];
+            // a non-finite or zero-energy rider has scale 0: its samples must not turn 0 * inf into NaN for the other rider
+            z[k] = mk2(rsa != (F)0 ? v.x * rsa : (F)0, rsb != (F)0 ? -(v.y * rsb) : (F)0);
         }
         pass1_table<S>(z, f0, sm, tw);
     }
