@@ -225,6 +225,8 @@ int nbls_memcpy_d2h(nbls_ctx* ctx, void* dst_host, const void* src_dev, size_t b
                                         max_screen_err then covers every lag, not only the maximum); slow, for tests */
 #define NBLS_OPT_FILTER_P1_WARPS 7   /* warps per block of the shared forward phase 1: 4 or 8; 0 (default) = automatic */
 #define NBLS_OPT_FILTER_P1_SUB 8     /* sub-chunks per chunk of the forward state pass: 1 (default, also 0), 2, 4 or 8 */
+#define NBLS_OPT_FILTER_OVERLAP 9    /* 1 (default): the filter runs two band groups side by side on two streams (the state
+                                        passes of the low bands hide under the output passes of the high bands); 0: one stream */
 #define NBLS_OPT_COUNT 16
 int nbls_set_option(nbls_ctx* ctx, int32_t key, int64_t value);
 int nbls_get_option(nbls_ctx* ctx, int32_t key, int64_t* value);

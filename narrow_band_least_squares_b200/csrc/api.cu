@@ -287,6 +287,7 @@ int nbls_create(nbls_ctx** out, int32_t device) {
     ctx->opt[NBLS_OPT_FILTER_SPLIT] = 1;
     ctx->opt[NBLS_OPT_FILTER_SHARED_P1] = 1;
     ctx->opt[NBLS_OPT_FILTER_LANES] = 131072;
+    ctx->opt[NBLS_OPT_FILTER_OVERLAP] = 1;
     *out = ctx;
     return NBLS_OK;
 }
@@ -308,6 +309,9 @@ int nbls_destroy(nbls_ctx* ctx) {
         if (ctx->pev[i]) cudaEventDestroy(ctx->pev[i]);
     for (int i = 0; i < 8; ++i)
         if (ctx->mark[i]) cudaEventDestroy(ctx->mark[i]);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return NBLS_OK;

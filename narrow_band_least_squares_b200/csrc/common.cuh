@@ -84,6 +84,8 @@ struct nbls_ctx {
     int sm_count = 0;
     size_t smem_optin = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;         // second stream of the filter (band groups side by side), created on first use
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     size_t ws_limit = 0;
     int64_t launches = 0;
     // cached buffers

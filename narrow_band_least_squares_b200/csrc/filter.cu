@@ -715,68 +715,67 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
     }
 
     const size_t smem = (size_t)FT_WARPS * FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
-    const dim3 grid((B + FT_WARPS - 1) / FT_WARPS, (nchunks + 31) / 32, C);
-    NBLS_REQUIRE(grid.y <= 65535, "nbls_filter: chunk grid too large (raise chunk_len)");
+    NBLS_REQUIRE((nchunks1 + 31) / 32 <= 65535, "nbls_filter: chunk grid too large (raise chunk_len)");
     for (int rev = 0; rev < 2; ++rev) {
         chunk_fn fn = pick(S, rev != 0);
         NBLS_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
+    bool mono = true;
+    for (int b = 1; b < B; ++b) mono = mono && hproc[B + b] <= hproc[B + b - 1];
 
-    // shared-read phase 1 of the forward pass: needs the bands' decay lengths to fall with the band index
-    // The bands are dealt to `nsplit` blocks per (32 chunks, channel) so that a warp carries at most three of them: a lane's
-    // recurrences are serial over the chunk, and the longest (lowest band, whole chunk) sets the kernel time.
-    state_fn shared_p1 = nullptr;
-    int nsplit = 1, p1_warps = 4;
-    {
-        bool mono = true;
-        for (int b = 1; b < B; ++b) mono = mono && hproc[B + b] <= hproc[B + b - 1];
-        nsplit = (int)std::max<int64_t>(1, ctx->opt[NBLS_OPT_FILTER_SPLIT]);
-        const int per_block = (B + nsplit - 1) / nsplit;
-        if (mono && nchunks > 1 && ctx->opt[NBLS_OPT_FILTER_SHARED_P1])
-        {
-            // warps per block: 8 when 4 would leave a warp with more than three bands (two sweeps per tile), else 4
-            p1_warps = (int)ctx->opt[NBLS_OPT_FILTER_P1_WARPS];
-            if (p1_warps != 4 && p1_warps != 8) p1_warps = ((per_block + 3) / 4 > 3) ? 8 : 4;
-            shared_p1 = pick_state(S, per_block, p1_warps);
-            if (!shared_p1 && p1_warps == 4) { p1_warps = 8; shared_p1 = pick_state(S, per_block, 8); }
-        }
-    }
-    auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper) -> int {
+    // One pass (forward or backward) over the bands [b0, b0 + nb) on stream `st`: state pass, carry, output pass.
+    auto run_pass = [&](bool rev, const double* in, int64_t in_row, int64_t in_band, bool taper, int b0, int nb,
+                        cudaStream_t st) -> int {
         chunk_fn fn = pick(S, rev);
-        FilterArgs a;
-        memset(&a, 0, sizeof(a));
-        a.in = in; a.in_row = in_row; a.in_band = in_band;
-        a.coef = dcoef; a.B = B; a.C = C; a.T = T;
-        // the state pass of the forward direction runs on sub-chunks (see above), the backward one on whole chunks
+        const dim3 grid((nb + FT_WARPS - 1) / FT_WARPS, (nchunks + 31) / 32, C);
+        // the state pass of the forward direction may run on sub-chunks (see above), the backward one on whole chunks
         const int psub = rev ? 1 : sub;
         const int pn = rev ? nchunks : nchunks1;
+        double* dstate_g = dstate ? dstate + (size_t)b0 * C * nchunks1 * S2 : nullptr;     // every band owns nchunks1 slots
+        FilterArgs a;
+        memset(&a, 0, sizeof(a));
+        a.in = in + (int64_t)b0 * in_band; a.in_row = in_row; a.in_band = in_band;
+        a.coef = dcoef + (size_t)b0 * S * 5; a.B = nb; a.C = C; a.T = T;
         if (nchunks > 1) {
             a.L = (int)(rev ? L : L1); a.nchunks = pn;
-            a.out = nullptr; a.proc_tiles = rev ? dproc : dproc1; a.state_in = nullptr; a.state_out = dstate;
+            a.out = nullptr; a.proc_tiles = (rev ? dproc : dproc1) + b0; a.state_in = nullptr; a.state_out = dstate_g;
             const dim3 grid1(grid.x, (pn + 31) / 32, C);
-            NBLS_REQUIRE(grid1.y <= 65535, "nbls_filter: chunk grid too large (raise chunk_len)");
             {
                 KernelGroupScope ks(ctx, rev ? KG_FILTER_P1B : KG_FILTER_P1F, 0.0);   // state passes: no algorithmic bytes
-                if (!rev && in_band == 0 && shared_p1) {
-                    // every band reads the same record: one read of each tile for all bands
+                // shared-read phase 1 of the forward pass (every band reads the same record: one read of each tile for all
+                // bands of the group); needs the bands' decay lengths to fall with the band index.  The bands can be dealt
+                // to `nsplit` blocks per (32 chunks, channel).
+                state_fn shared_p1 = nullptr;
+                int p1_warps = 4;
+                const int nsplit = (int)std::max<int64_t>(1, ctx->opt[NBLS_OPT_FILTER_SPLIT]);
+                if (!rev && in_band == 0 && mono && ctx->opt[NBLS_OPT_FILTER_SHARED_P1]) {
+                    const int per_block = (nb + nsplit - 1) / nsplit;
+                    // warps per block: 8 when 4 would leave a warp with more than three bands (two sweeps per tile), else 4
+                    p1_warps = (int)ctx->opt[NBLS_OPT_FILTER_P1_WARPS];
+                    if (p1_warps != 4 && p1_warps != 8) p1_warps = ((per_block + 3) / 4 > 3) ? 8 : 4;
+                    shared_p1 = pick_state(S, per_block, p1_warps);
+                    if (!shared_p1 && p1_warps == 4) { p1_warps = 8; shared_p1 = pick_state(S, per_block, 8); }
+                }
+                if (shared_p1) {
                     const size_t smem1 = (size_t)FT_STAGES * FT_TILE_DOUBLES * sizeof(double);
                     a.nsplit = nsplit;
-                    shared_p1<<<dim3(grid1.y, C, nsplit), p1_warps * 32, smem1, ctx->stream>>>(a);
+                    shared_p1<<<dim3(grid1.y, C, nsplit), p1_warps * 32, smem1, st>>>(a);
                 } else {
-                    fn<<<grid1, FT_WARPS * 32, smem, ctx->stream>>>(a);
+                    fn<<<grid1, FT_WARPS * 32, smem, st>>>(a);
                 }
             }
             NBLS_CUDA(cudaGetLastError());
             {
                 KernelGroupScope ks(ctx, KG_FILTER_CARRY, 0.0);
-                pick_carry(S)<<<(B * C + 31) / 32, 32, 0, ctx->stream>>>(dstate, rev ? dml : dml1, B, C, pn, rev ? 1 : 0);
+                pick_carry(S)<<<(nb * C + 31) / 32, 32, 0, st>>>(dstate_g, (rev ? dml : dml1) + (size_t)b0 * S2 * S2, nb, C, pn,
+                                                                 rev ? 1 : 0);
             }
             NBLS_CUDA(cudaGetLastError());
             ctx->launches += 2;
         }
         a.L = (int)L; a.nchunks = nchunks;
-        a.out = y; a.out_row = ldy; a.out_band = ystride_band;
-        a.proc_tiles = nullptr; a.state_in = nchunks > 1 ? dstate : nullptr; a.state_out = nullptr;
+        a.out = y + (int64_t)b0 * ystride_band; a.out_row = ldy; a.out_band = ystride_band;
+        a.proc_tiles = nullptr; a.state_in = nchunks > 1 ? dstate_g : nullptr; a.state_out = nullptr;
         a.sin_n = pn; a.sin_mul = psub; a.sin_off = 0;
         if (taper) {
             a.taper_up = dup; a.taper_down = ddown; a.taper_len = d->taper_len; a.g0 = d->global_t0;
@@ -784,17 +783,48 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         }
         {
             // algorithmic bytes: the raw record is read once for all bands (in_band == 0), a filtered band once; one write
-            const double rd = in_band == 0 ? 8.0 * C * (double)T : 8.0 * B * C * (double)T;
-            KernelGroupScope ks(ctx, rev ? KG_FILTER_P3B : KG_FILTER_P3F, rd + 8.0 * B * C * (double)T);
-            fn<<<grid, FT_WARPS * 32, smem, ctx->stream>>>(a);
+            const double rd = in_band == 0 ? 8.0 * C * (double)T * nb / B : 8.0 * nb * C * (double)T;
+            KernelGroupScope ks(ctx, rev ? KG_FILTER_P3B : KG_FILTER_P3F, rd + 8.0 * nb * C * (double)T);
+            fn<<<grid, FT_WARPS * 32, smem, st>>>(a);
         }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 1;
         return NBLS_OK;
     };
+    auto run_group = [&](int b0, int nb, cudaStream_t st) -> int {
+        NBLS_CHECK(run_pass(false, x, ldx, 0, !d->zerophase, b0, nb, st));
+        if (d->zerophase) NBLS_CHECK(run_pass(true, y, ldy, ystride_band, true, b0, nb, st));
+        return NBLS_OK;
+    };
 
-    NBLS_CHECK(run_pass(false, x, ldx, 0, !d->zerophase));
-    if (d->zerophase) NBLS_CHECK(run_pass(true, y, ldy, ystride_band, true));
+    // Two band groups on two streams: the state passes are bound by FP64 work at low occupancy (the forward one runs 225
+    // blocks on 148 SMs), the output passes by HBM bandwidth - side by side the low group's state passes hide under the
+    // high group's output passes.  The low group holds the bands whose state passes are long (it is enqueued first, so
+    // its few blocks are resident before the other stream fills the SMs).  Not in profile mode: there every group is
+    // timed on its own.
+    int b_lo = 0;
+    if (d->zerophase && nchunks > 1 && B >= 8 && ctx->opt[NBLS_OPT_FILTER_OVERLAP] && !ctx->opt[NBLS_OPT_PROFILE]) {
+        int64_t tot = 0, acc = 0;
+        for (int b = 0; b < B; ++b) tot += hproc[b];
+        // low group = the bands that hold ~40 % of the state-pass work (option values >= 10 give the percentage), at
+        // least 2 and at most B - 2 bands.  Measured on c3/24 h (filter stage, ms): one stream 28.04; 12-30 % 28.1-27.8;
+        // 40 % 26.3-26.4; 55 % 26.8; 70 % 26.9; 85-95 % 27.5
+        const int64_t pct = ctx->opt[NBLS_OPT_FILTER_OVERLAP] >= 10 ? std::min<int64_t>(95, ctx->opt[NBLS_OPT_FILTER_OVERLAP]) : 40;
+        for (b_lo = 0; b_lo < B && acc * 100 < tot * pct; ++b_lo) acc += hproc[b_lo];
+        b_lo = std::max(2, std::min(B - 2, b_lo));
+    }
+    if (b_lo == 0) return run_group(0, B, ctx->stream);
+    if (!ctx->stream2) {
+        NBLS_CUDA(cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+        NBLS_CUDA(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+        NBLS_CUDA(cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    }
+    NBLS_CUDA(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    NBLS_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+    NBLS_CHECK(run_group(0, b_lo, ctx->stream));
+    NBLS_CHECK(run_group(b_lo, B - b_lo, ctx->stream2));
+    NBLS_CUDA(cudaEventRecord(ctx->ev_join, ctx->stream2));
+    NBLS_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     return NBLS_OK;
 }
 
