@@ -1013,6 +1013,9 @@ def main():
             "clocks": r["clocks"], "gpu_launches": int(r["launches"]), "e2e": r["e2e"],
             "stage_ms": r["stage"], "gather_ms": r["gather_ms"], "wall_ms_per_step": r["wall_ms"] / args.steps,
             "roofline": roof, "kernel_groups": groups,
+            "kernel_groups_note": ("one extra step with NBLS_OPT_PROFILE: a CUDA-event pair around every kernel group, the "
+                                   "filter's two band groups run one after the other there (in the timed steps they overlap "
+                                   "on two streams, so stage_ms.filter is smaller than the sum of its groups)"),
             "roofline_filter": {"kernel": "biquad_state_shared_kernel + biquad_chunk_kernel x3 + carry_kernel x2",
                                 "bound": "hbm", "achieved": fgb, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                 "frac": (fgb / peaks["hbm_gbs"]) if fgb else None, "peak_source": peak_src,

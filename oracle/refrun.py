@@ -5,9 +5,10 @@ product package imports this module.
 
 The reference (amiezzi/narrow_band_least_squares) is pure Python, so "building" it for the GPU box means putting
 the handful of files its hot path imports where the box can see them: ``stage_reference()`` — called from
-``__graft_entry__.build()`` whenever /root/reference is present — copies them into the git-ignored ``oracle/_ref/``
-(never into the tracked tree; ``oracle/_ref/`` travels with gpurun like a built .so).  ``import_reference()`` then
-imports them unmodified through the import shims of ``oracle/refstubs`` (obspy / matplotlib stand-ins, SURVEY.md
+``__graft_entry__.build()`` whenever /root/reference is present — packs them into the git-ignored archive
+``oracle/_ref/reference_hotpath.zip`` (a build artefact: never in the tracked tree, it travels with gpurun like a built
+.so and is executed straight from the archive with zipimport).  ``import_reference()`` then imports the reference
+unmodified through the import shims of ``oracle/refstubs`` (obspy / matplotlib stand-ins, SURVEY.md
 Appendix A.5) and replaces the module-local ``np`` of narrow_band_least_squares.py by a proxy that maps the
 ``'complex_'`` dtype string numpy >= 2 removed (narrow_band_least_squares.py:58-59,276-277) to complex128.
 """
@@ -21,6 +22,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 STAGED = os.path.join(HERE, "_ref")
+ARCHIVE = os.path.join(STAGED, "reference_hotpath.zip")      # the build artefact: imported with zipimport, never unpacked
 # files on the hot path; plotting, waveform download and docs are not staged
 HOT_PATH_FILES = (
     "narrow_band_least_squares.py",
@@ -36,26 +38,38 @@ HOT_PATH_FILES = (
 
 
 def reference_dir():
-    """The reference tree to execute: $NBLS_REFERENCE, /root/reference (build container), else oracle/_ref."""
-    for d in (os.environ.get("NBLS_REFERENCE"), "/root/reference", STAGED):
+    """The reference to execute: $NBLS_REFERENCE, /root/reference (build container), else the staged archive
+    oracle/_ref/reference_hotpath.zip (a path Python's zipimport accepts like a directory)."""
+    for d in (os.environ.get("NBLS_REFERENCE"), "/root/reference"):
         if d and os.path.isfile(os.path.join(d, "narrow_band_least_squares.py")):
             return d
+    if os.path.isfile(ARCHIVE):
+        return ARCHIVE
     return None
 
 
-def stage_reference(src="/root/reference", dst=STAGED):
-    """Copy the reference's hot-path files from ``src`` to the git-ignored ``dst``.  Returns the number copied
-    (0 if ``src`` does not exist, e.g. on the GPU box, where the staged copy arrives with the snapshot)."""
+def stage_reference(src="/root/reference", dst=ARCHIVE):
+    """Pack the reference's hot-path files from ``src`` into the git-ignored archive ``dst`` (the "built" reference that
+    travels to the GPU box; it is executed from the archive, unmodified, and never enters the tracked tree).  Returns the
+    number of files packed (0 if ``src`` does not exist, e.g. on the GPU box, where the archive arrives with the snapshot)."""
+    import zipfile
     if not os.path.isfile(os.path.join(src, "narrow_band_least_squares.py")):
         return 0
+    os.makedirs(os.path.dirname(dst), exist_ok=True)
+    for stale in HOT_PATH_FILES:                     # loose copies of an earlier layout
+        f = os.path.join(os.path.dirname(dst), stale)
+        if os.path.isfile(f):
+            os.remove(f)
+    shutil.rmtree(os.path.join(os.path.dirname(dst), "lts_array"), ignore_errors=True)
     n = 0
-    for rel in HOT_PATH_FILES:
-        s, d = os.path.join(src, rel), os.path.join(dst, rel)
-        if not os.path.isfile(s):
-            continue
-        os.makedirs(os.path.dirname(d), exist_ok=True)
-        shutil.copyfile(s, d)
-        n += 1
+    tmp = dst + ".tmp"
+    with zipfile.ZipFile(tmp, "w", zipfile.ZIP_DEFLATED) as z:
+        for rel in HOT_PATH_FILES:
+            s = os.path.join(src, rel)
+            if os.path.isfile(s):
+                z.write(s, rel)
+                n += 1
+    os.replace(tmp, dst)
     return n
 
 
