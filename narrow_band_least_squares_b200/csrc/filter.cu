@@ -236,14 +236,14 @@ __global__ void __launch_bounds__(FT_WARPS * 32) biquad_chunk_kernel(FilterArgs 
     // this launch, none of its samples lies in the first / last taper_len samples of the global record
     const int64_t s_lo = chunk0 * a.L, s_hi = (chunk0 + 32) * a.L;          // local sample range [s_lo, s_hi)
     const bool edge = s_hi > a.T;
-    const bool tapered = a.out && a.taper_len > 0 &&
-                         ((a.g0 + s_lo < a.taper_len) || (a.g0 + s_hi > a.G - a.taper_len));
+    (void)s_lo;
     if (!a.out) {     // phase 1: chunk end states only
         if (edge) biquad_warp<S, REV, 2, true, true>(a, ring, band, chan, chunk0, lane);
         else biquad_warp<S, REV, 0, true, true>(a, ring, band, chan, chunk0, lane);
     } else if (a.nchunks > 1) {
+        // whole chunks take the interior path even inside a taper zone: taper_rmw_kernel multiplies the ramps in
+        // afterwards (the ragged last warp tapers its own samples)
         if (edge) biquad_warp<S, REV, 2, false, true>(a, ring, band, chan, chunk0, lane);
-        else if (tapered) biquad_warp<S, REV, 1, false, true>(a, ring, band, chan, chunk0, lane);
         else biquad_warp<S, REV, 0, false, true>(a, ring, band, chan, chunk0, lane);
     } else {
         biquad_warp<S, REV, 2, false, false>(a, ring, band, chan, chunk0, lane);
@@ -400,6 +400,23 @@ __global__ void __launch_bounds__(FS_WARPS * 32, 512 / (FS_WARPS * 32)) biquad_s
                 for (int s_ = 0; s_ < S; ++s_) { a.state_out[sidx + 2 * s_] = z0[q][s_]; a.state_out[sidx + 2 * s_ + 1] = z1[q][s_]; }
             }
         }
+    }
+}
+
+// The Hann ramps of obspy's taper over the whole chunks of a multi-chunk run: y[t] *= ramp[g0 + t] for the local samples
+// t < t_end that lie in the first / last taper_len samples of the GLOBAL record.  (Fused into the output pass these
+// multiplies - two dependent table loads in front of every 16-byte store - cost the edge ranks of a time-sharded 8 x 24 h
+// record 4.5 ms of a 12.8 ms kernel; as a read-modify-write over the zones alone they cost the zone's traffic.)  The same
+// __dmul_rn as the fused path: identical bits.  grid = (blocks over the zone, C, bands); zone 0 = head, 1 = tail.
+__global__ void __launch_bounds__(256) taper_rmw_kernel(double* y, int64_t row, int64_t band, int C, const double* up,
+                                                        const double* down, int64_t taper_len, int64_t g0, int64_t G,
+                                                        int64_t t_lo, int64_t t_hi, int zone) {
+    const int b = blockIdx.z, c = blockIdx.y;
+    (void)C;
+    double* p = y + (int64_t)b * band + (int64_t)c * row;
+    for (int64_t t = t_lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < t_hi; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t g = g0 + t;
+        p[t] = __dmul_rn(p[t], zone == 0 ? up[g] : down[g - (G - taper_len)]);
     }
 }
 
@@ -789,6 +806,23 @@ int filter_impl(nbls_ctx* ctx, const nbls_filter_desc* d, const double* x, int C
         }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 1;
+        if (taper && d->taper_len > 0 && nchunks > 1) {
+            // whole chunks were written untapered: local samples [0, t_whole) of the two global taper zones
+            const int64_t t_whole = std::min<int64_t>(T, (T / (32 * L)) * (32 * L));      // below the ragged last warp
+            const int64_t G = a.G, g0 = a.g0, wl = d->taper_len;
+            const int64_t h_lo = 0, h_hi = std::min<int64_t>(t_whole, wl - g0);                         // g < wl
+            const int64_t t_lo2 = std::max<int64_t>(0, G - wl - g0), t_hi2 = std::min<int64_t>(t_whole, G - g0);   // g >= G - wl
+            for (int zone = 0; zone < 2; ++zone) {
+                const int64_t lo = zone == 0 ? h_lo : t_lo2, hi = zone == 0 ? h_hi : t_hi2;
+                if (hi <= lo) continue;
+                KernelGroupScope ks(ctx, rev ? KG_FILTER_P3B : KG_FILTER_P3F, 0.0);
+                const unsigned gx = (unsigned)std::min<int64_t>(1024, (hi - lo + 255) / 256);
+                taper_rmw_kernel<<<dim3(gx, (unsigned)C, (unsigned)nb), 256, 0, st>>>(a.out, ldy, ystride_band, C, dup, ddown, wl, g0, G,
+                                                                           lo, hi, zone);
+                NBLS_CUDA(cudaGetLastError());
+                ctx->launches += 1;
+            }
+        }
         return NBLS_OK;
     };
     auto run_group = [&](int b0, int nb, cudaStream_t st) -> int {
