@@ -71,9 +71,8 @@ __device__ __forceinline__ void cp_async_wait() {
 }
 
 // One warp, 32 consecutive chunks of one (band, channel).  MODE 0 is the interior fast path: every chunk of the warp is
-// whole and no sample lies in the taper zones, so loads and stores carry no bounds or taper logic.  MODE 1: whole chunks
-// inside a taper zone - no bounds logic, the stores multiply by the ramp (the first / last 1 % of a LONG record is many
-// chunks: on the edge ranks of a time-sharded run it used to cost 9 ms of a 29 ms filter).  MODE 2: ragged record end.
+// whole, so loads and stores carry no bounds or taper logic (the Hann ramps of whole chunks are multiplied in afterwards by
+// taper_rmw_kernel).  MODE 2: the ragged record end (or a single-chunk run): bounds checks, taper fused into the store.
 template <int S, bool REV, int MODE, bool STATE_ONLY, bool FUSED>
 __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, int band, int chan, int64_t chunk0,
                                             int lane) {
@@ -187,14 +186,6 @@ __device__ __forceinline__ void biquad_warp(const FilterArgs& a, double* ring, i
                 double2 d = *reinterpret_cast<const double2*>(srow + q * FT_ROWS_PER_REQ * FT_ROW);
                 const int64_t t = t0 + q * slot_stride;
                 if constexpr (MODE == 0) {
-                    *reinterpret_cast<double2*>(out + t) = d;
-                } else if constexpr (MODE == 1) {
-                    const int64_t g = a.g0 + t;
-                    const int64_t dn = a.G - a.taper_len;
-                    if (g < a.taper_len) d.x = __dmul_rn(d.x, a.taper_up[g]);
-                    if (g + 1 < a.taper_len) d.y = __dmul_rn(d.y, a.taper_up[g + 1]);
-                    if (g >= dn) d.x = __dmul_rn(d.x, a.taper_down[g - dn]);
-                    if (g + 1 >= dn) d.y = __dmul_rn(d.y, a.taper_down[g + 1 - dn]);
                     *reinterpret_cast<double2*>(out + t) = d;
                 } else {
                     const int64_t k = chunk0 + row0 + q * FT_ROWS_PER_REQ;
