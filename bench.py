@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--hours", type=float, default=None, help="record length (default: the workload's)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--narrays", type=int, default=None, help="c5: arrays in the batch (default 64)")
+    ap.add_argument("--alpha", type=float, default=None, help="override the workload's ALPHA (1.0 = OLS, [0.5, 1) = FAST-LTS)")
     ap.add_argument("--method", default="auto", choices=["auto", "direct", "fft", "fft64", "fft32"])
     ap.add_argument("--max-lag", type=int, default=-1, help="restrict |lag| (default: all 2N-1 lags = reference)")
     ap.add_argument("--single-stage", action="store_true", help="switch the two-stage lag search off")
@@ -156,6 +157,8 @@ def workload(args):
     from narrow_band_least_squares_b200.configs import config_job
     j = config_job(args.workload)
     j["hours_total"] = j["hours"] if args.hours is None else args.hours
+    if args.alpha is not None:
+        j["alpha"] = args.alpha
     j["narrays"] = (args.narrays or 64) if args.workload == "c5" else 1
     return j
 

@@ -140,13 +140,64 @@ __device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, 
     }
     if (lane == 0 && (P & 1)) key[P] = hnan;      // pad to a whole half2: NaN compares false
     __syncwarp();
+    bool in[NI];
+    if constexpr (NI >= 4) {
+        // P > 96: instead of counting every key against every key (P^2 / 64 half2 compares per lane), SELECT the h-th
+        // smallest key K* = min{v : #{key <= v} >= h} bit by bit over the 15-bit pattern of a non-negative FP16 (patterns
+        // order like values): 15 warp-wide counts of NI ballots each.  Keys below K* are in the subset, keys above are
+        // not, and the tie group at K* is in as a whole if it ends exactly at rank h - otherwise it straddles the
+        // boundary and its members are ranked with the exact FP64 rule, as below.  Same subset as the counting form.
+        // (NaN residuals - a NaN fit - get pattern 0: they are in the subset either way and make the sums NaN.)
+        unsigned ku[NI];
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            const int p = lane + 32 * i;
+            const unsigned b = (unsigned)__half_as_ushort(__low2half(kp[i]));
+            ku[i] = p < P ? (b > 0x7C00u ? 0u : b) : 0xFFFFu;
+        }
+        unsigned kstar = 0;
+#pragma unroll
+        for (int bit = 14; bit >= 0; --bit) {
+            const unsigned t = kstar | ((1u << bit) - 1u);
+            int c = 0;
+#pragma unroll
+            for (int i = 0; i < NI; ++i) c += __popc(__ballot_sync(0xffffffffu, ku[i] <= t));
+            if (c < h) kstar |= 1u << bit;
+        }
+        int c_lt = 0, c_le = 0;
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            c_lt += __popc(__ballot_sync(0xffffffffu, ku[i] < kstar));
+            c_le += __popc(__ballot_sync(0xffffffffu, ku[i] <= kstar));
+        }
+        const bool whole = c_le == h;           // the tie group at K* ends exactly at rank h
+#pragma unroll
+        for (int i = 0; i < NI; ++i) in[i] = ku[i] < kstar || (whole && ku[i] == kstar);
+        if (!whole) {                           // warp-uniform: the tie group straddles the boundary
+            const int need = h - c_lt;
+#pragma unroll
+            for (int i = 0; i < NI; ++i) {
+                const int p = lane + 32 * i;
+                if (ku[i] == kstar) {
+                    int r = 0;
+                    for (int q = 0; q < P; ++q) {
+                        const unsigned bq = (unsigned)keyb[q];
+                        if ((bq > 0x7C00u ? 0u : bq) == kstar) {
+                            const double u = absr[q];
+                            r += (u < v[i]) || (u == v[i] && q < p);
+                        }
+                    }
+                    in[i] = r < need;
+                }
+            }
+        }
+    } else {
     const int P2 = (P + 1) >> 1;
     for (int q2 = 0; q2 < P2; ++q2) {
         const __half2 kq = key2[q2];
 #pragma unroll
         for (int i = 0; i < NI; ++i) cnt[i] = __hadd2(cnt[i], __hle2(kq, kp[i]));
     }
-    bool in[NI];
     int n_in = 0;
 #pragma unroll
     for (int i = 0; i < NI; ++i) {
@@ -178,6 +229,7 @@ __device__ __forceinline__ Sums rank_pass16(const double* x0, const double* x1, 
                 in[i] = r < need;
             }
         }
+    }
     }
     Sums s = {0, 0, 0, 0, 0, 0};
 #pragma unroll

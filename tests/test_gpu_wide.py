@@ -74,10 +74,13 @@ def _oracle_lts_chunk(tau, mad, xij, xij_std, xij_mad, alpha, h):
     return orc.lts_post(tau, xij, coeffs, alpha, h)
 
 
-@pytest.mark.parametrize("nchans,alpha,aperture", [(6, 0.75, 0.5), (12, 0.5, 0.8)], ids=["P15_a075", "P66_a05"])
-def test_lts_flags_bit_exact_over_5000_windows(eng, nchans, alpha, aperture):
+@pytest.mark.parametrize("nchans,alpha,aperture,nwin", [(6, 0.75, 0.5, 5120), (12, 0.5, 0.8, 5120), (25, 0.6, 1.0, 96)],
+                         ids=["P15_a075", "P66_a05", "P300_a06"])
+def test_lts_flags_bit_exact_over_5000_windows(eng, nchans, alpha, aperture, nwin):
+    """P = 15: one key per lane, rank counting; P = 66: three keys per lane, rank counting; P = 300 (a
+    25-element array, fewer windows: the oracle needs ~2 s per window there): ten keys per lane, the h-th key by radix select."""
     from joblib import Parallel, delayed
-    fs, nwin = 100.0, 5120
+    fs = 100.0
     rij, co, lag = synth_lags(4000 + nchans, nchans, aperture, fs, nwin)
     p = lag.shape[1]
     cmax = np.full((nwin, p), 0.5)
@@ -93,7 +96,7 @@ def test_lts_flags_bit_exact_over_5000_windows(eng, nchans, alpha, aperture):
     vel = np.concatenate([q[0] for q in parts]); baz = np.concatenate([q[1] for q in parts])
     sig = np.concatenate([q[2] for q in parts]); wts = np.concatenate([q[3] for q in parts], axis=1)
     skipped = (mad == 0) | (np.count_nonzero(tau, axis=0) < p - 2)
-    assert 0 < skipped.sum() < nwin // 4
+    assert 0 < skipped.sum() < nwin // 2
     bad = np.where(np.any(got["weights"].T != wts, axis=0))[0]
     assert bad.size == 0, (f"LTS flags differ in {bad.size} of {nwin} windows (P={p}, h={h}); first: {bad[:8]}, "
                            f"modes {bad[:8] % 8}")
