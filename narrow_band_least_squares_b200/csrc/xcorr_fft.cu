@@ -519,15 +519,32 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         for (int i = 1; i < T / 32; ++i) { mr = fmaxf(mr, smax[0][i]); mi = fmaxf(mi, smax[1][i]); }
         const float thr_r = mr - XF_TAU32 * (float)L, thr_i = mi - XF_TAU32 * (float)L;
         if ((lmr >= thr_r) | (lmi >= thr_i)) {      // warp-uniform: only warps holding a value inside the band rescan
+            // The unrolled part only builds two hit masks (z[] lives in registers, so n3 must be a constant); the rare hits
+            // are then handled by a rolled loop.  One warp of every CTA comes through here with a cold instruction cache
+            // while the other warps wait at the barrier below, so this code has to stay small.
+            static_assert(S::R3 <= 32, "one mask bit per pass-3 output");
+            unsigned hbr = 0u, hbi = 0u;
 #pragma unroll
             for (int n3 = 0; n3 < S::R3; ++n3) {
-                const bool ok = (n3 <= n3a) | (n3 >= n3b);
-                const bool hr = ok & (z[n3].x >= thr_r), hi = ok & (z[n3].y >= thr_i);
-                if (hr | hi) {
+                hbr |= (z[n3].x >= thr_r ? 1u : 0u) << n3;
+                hbi |= (z[n3].y >= thr_i ? 1u : 0u) << n3;
+            }
+            unsigned okm = 0u;                         // wanted n3: [0, n3a] and [n3b, R3)
+            if (n3a >= 0) okm |= n3a >= 31 ? 0xffffffffu : ((2u << n3a) - 1u);
+            if (n3b < S::R3) okm |= n3b <= 0 ? 0xffffffffu : ~((1u << n3b) - 1u);
+            if (S::R3 < 32) okm &= (1u << (S::R3 & 31)) - 1u;
+            hbr &= okm;
+            hbi &= okm;
+#pragma unroll 1
+            for (int c = 0; c < 2; ++c) {
+                unsigned hb = c == 0 ? hbr : hbi;
+                while (hb) {
+                    const int n3 = __ffs(hb) - 1;
+                    hb &= hb - 1u;
                     const int n = nb + STEP * n3;
                     const int lg = n <= lag_max ? n : n - L;
-                    if (hr) { const int s_ = atomicAdd(&scnt[0], 1); if (s_ < XF_KC) scl[0][s_] = lg; }
-                    if (hi) { const int s_ = atomicAdd(&scnt[1], 1); if (s_ < XF_KC) scl[1][s_] = lg; }
+                    const int s_ = atomicAdd(&scnt[c], 1);
+                    if (s_ < XF_KC) scl[c][s_] = lg;
                 }
             }
         }
