@@ -266,6 +266,26 @@ int nbls_measure_fp32_peak(nbls_ctx* ctx, int32_t iters, double* tflops);
 int nbls_experiment_dft_pass(nbls_ctx* ctx, int32_t mode, const float* x_dev, int64_t rows, int32_t reps, int32_t iters,
                              float* y_dev, float* ms);
 
+/* ---- allocation-free cross-correlation ------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid allocation).
+ * Time-domain FP64 cross-correlation of ONE band (the tiled kernel pair nbls_xcorr uses for long windows: same lags, same
+ * tie rule, same cmax), whose scratch - one partial maximum per (window, pair, block of 2048 lags) - lives in a
+ * file-scope `static __device__` array of the library instead of the context's growable workspace.  The call performs no
+ * cudaMalloc / cudaFree and calls no allocating routine; it enqueues two kernels on the context's stream and returns.
+ *   y_dev [nchan][ldy] filtered band (device); windows w = 0..win_count-1 start at win_first + w*win_hop, win_len samples
+ *   max_lag as in nbls_window_desc; lag_dev [win_count][P] int32, cmax_dev [win_count][P] double or NULL (device)
+ * Limit: win_count * P * ceil((2*L+1)/2048) <= NBLS_XCORR_STATIC_MAX_ENTRIES (L = the lag bound searched, win_len-1 for
+ * max_lag < 0); larger requests fail with NBLS_ERR_* and a message, nothing is launched - split the windows over
+ * several calls or use nbls_xcorr.  The array (3 MiB) is held by every GPU that loads the library until exit and is
+ * SHARED by all calls and contexts on a GPU: calls that overlap on the GPU (different contexts/streams) race; calls on
+ * one context are ordered by its stream.  The array keeps the last call's contents; nothing in it needs clearing (every
+ * entry is written before it is read).  The first call on a device looks the array's address up (cudaGetSymbolAddress,
+ * no allocation); make one call per device at set-up if later calls run under stream capture. */
+#define NBLS_XCORR_STATIC_MAX_ENTRIES 262144
+int nbls_xcorr_static(nbls_ctx* ctx, const double* y_dev, int32_t nchan, int64_t ldy, int32_t win_len, int32_t win_hop,
+                      int64_t win_first, int32_t win_count, int32_t max_lag, int32_t* lag_dev, double* cmax_dev);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,6 +100,8 @@ EXPORTS = {
     "nbls_launch_count": (C.c_int64, [C.c_void_p]),
     "nbls_experiment_dft_pass": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p,
                                            C.POINTER(C.c_float)]),
+    "nbls_xcorr_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_int32, C.c_int32, C.c_int64, C.c_int32,
+                                    C.c_int32, C.c_void_p, C.c_void_p]),
     "nbls_measure_fp64_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
     "nbls_measure_fp32_peak": (C.c_int, [C.c_void_p, C.c_int32, c_double_p]),
 }

@@ -22,6 +22,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -400,4 +401,74 @@ int xcorr_direct_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, in
     return NBLS_OK;
 }
 
+// ---- allocation-free variant (nbls_xcorr_static) -------------------------------------------
+// The tiled kernels above with their [item][lag block] partial table in a file-scope device array instead of the
+// context's growable scratch buffer: for callers that may not allocate (CUDA graph capture, serving loops).  Every GPU
+// that loads the library holds the array (3 MiB) until exit.  In host code the array's NAME is only a stand-in for the
+// symbol; the device address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// All calls share the array: two calls that overlap on the GPU (different streams / contexts) race.  Nothing in it has
+// to start at zero: xcorr_long_kernel writes every (item, block) entry before xcorr_long_finish_kernel reads it.
+constexpr size_t XS_BYTES = (size_t)NBLS_XCORR_STATIC_MAX_ENTRIES * (sizeof(double) + sizeof(int));
+static __device__ __align__(256) unsigned char xs_scratch[XS_BYTES];
+
+constexpr int XS_MAX_DEVICES = 64;
+static void* xs_addr[XS_MAX_DEVICES];       // device address of xs_scratch on each device, nullptr until looked up
+static std::mutex xs_mutex;
+
+// the caller has made `device` current
+static int xs_scratch_address(int device, void** out) {
+    NBLS_REQUIRE(device >= 0 && device < XS_MAX_DEVICES, "nbls_xcorr_static: device %d out of range", device);
+    std::lock_guard<std::mutex> lock(xs_mutex);
+    if (!xs_addr[device]) {
+        void* p = nullptr;
+        NBLS_CUDA(cudaGetSymbolAddress(&p, xs_scratch));
+        NBLS_REQUIRE(p, "nbls_xcorr_static: no device address for the static scratch array on device %d", device);
+        xs_addr[device] = p;
+    }
+    *out = xs_addr[device];
+    return NBLS_OK;
+}
+
+static int xcorr_static_impl(nbls_ctx* ctx, const double* y_dev, int C, int64_t ldy, int N, int hop, int64_t first, int W,
+                             int max_lag, int32_t* lag_dev, double* cmax_dev) {
+    NBLS_REQUIRE(ctx, "nbls_xcorr_static: null context");
+    NBLS_REQUIRE(y_dev && lag_dev, "nbls_xcorr_static: null input or output pointer");
+    NBLS_REQUIRE(C >= 2 && N >= 1 && hop >= 1 && W >= 0 && first >= 0, "nbls_xcorr_static: bad sizes (nchan %d, win_len %d, "
+                 "win_hop %d, win_count %d, win_first %lld)", C, N, hop, W, (long long)first);
+    NBLS_REQUIRE(first + (int64_t)(W > 0 ? W - 1 : 0) * hop + N <= ldy, "nbls_xcorr_static: the last window ends after ldy = %lld",
+                 (long long)ldy);
+    if (W == 0) return NBLS_OK;
+    NBLS_CUDA(cudaSetDevice(ctx->device));
+    const int P = C * (C - 1) / 2;
+    XlArgs a;
+    memset(&a, 0, sizeof(a));
+    a.y = y_dev; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first;
+    a.lag_max = (max_lag < 0 || max_lag > N - 1) ? N - 1 : max_lag;
+    a.nblk = (2 * a.lag_max + 1 + XL_LAGS - 1) / XL_LAGS;
+    const int64_t entries = (int64_t)W * P * a.nblk;
+    NBLS_REQUIRE(entries <= NBLS_XCORR_STATIC_MAX_ENTRIES,
+                 "nbls_xcorr_static: %d windows x %d pairs x %d lag blocks = %lld partial results exceed the static scratch "
+                 "array (NBLS_XCORR_STATIC_MAX_ENTRIES = %d); split the windows over several calls or use nbls_xcorr",
+                 W, P, a.nblk, (long long)entries, NBLS_XCORR_STATIC_MAX_ENTRIES);
+    void* scratch = nullptr;
+    NBLS_CHECK(xs_scratch_address(ctx->device, &scratch));
+    a.part_v = static_cast<double*>(scratch);
+    a.part_l = reinterpret_cast<int*>(a.part_v + NBLS_XCORR_STATIC_MAX_ENTRIES);
+    a.lag = lag_dev;
+    a.cmax = cmax_dev;
+    xcorr_long_kernel<<<(unsigned)entries, XL_THREADS, 0, ctx->stream>>>(a);
+    NBLS_CUDA(cudaGetLastError());
+    xcorr_long_finish_kernel<<<(unsigned)((int64_t)W * P), 256, 0, ctx->stream>>>(a);
+    NBLS_CUDA(cudaGetLastError());
+    ctx->launches += 2;
+    return NBLS_OK;
+}
+
 }  // namespace nbls
+
+extern "C" int nbls_xcorr_static(nbls_ctx* ctx, const double* y_dev, int32_t nchan, int64_t ldy, int32_t win_len,
+                                 int32_t win_hop, int64_t win_first, int32_t win_count, int32_t max_lag, int32_t* lag_dev,
+                                 double* cmax_dev) {
+    return nbls::xcorr_static_impl(ctx, y_dev, nchan, ldy, win_len, win_hop, win_first, win_count, max_lag, lag_dev,
+                                   cmax_dev);
+}
