@@ -77,6 +77,43 @@ template <class V> __device__ __forceinline__ V cmul(V a, V b) {
 template <class V> __device__ __forceinline__ V cmulc(V a, V b) {
     return mk2(fmad(a.x, b.x, a.y * b.y), fmad(a.y, b.x, -(a.x * b.y)));
 }
+// i * a
+template <class V> __device__ __forceinline__ V cmul_i(V a) { return mk2(-a.y, a.x); }
+// a + i b  and  conj(a) + i conj(b)
+template <class V> __device__ __forceinline__ V cadd_i(V a, V b) { return mk2(a.x - b.y, a.y + b.x); }
+template <class V> __device__ __forceinline__ V cadd_i_conj(V a, V b) { return mk2(a.x + b.y, b.x - a.y); }
+// half-by-half product
+template <class V> __device__ __forceinline__ V cmul_elem(V a, V b) { return mk2(a.x * b.x, a.y * b.y); }
+// c * t  and  a + c * t  with a real c
+template <class V> __device__ __forceinline__ V cscale(real_t<V> c, V t) { return mk2(c * t.x, c * t.y); }
+template <class V> __device__ __forceinline__ V caxpy(real_t<V> c, V t, V a) {
+    return mk2(fmad(c, t.x, a.x), fmad(c, t.y, a.y));
+}
+
+// ---- FP32: the same operations on the packed instructions of sm_100 (FADD2 / FMUL2 / FFMA2) ---------------------
+// A complex FP32 number is a register pair (re, im) and the packed instructions work on both halves in ONE issue slot;
+// their operands take a half swap (.LO_HI), a per-half negation and a scalar broadcast for free, which is all complex
+// arithmetic needs (times i = swap + negate one half).  Every overload below performs, half by half, exactly the
+// operations of its generic twin above (same products, same fused multiply-adds, IEEE round-to-nearest), so the FP32
+// transforms are bit-identical to the scalar formulation at half the floating-point instruction count.
+__device__ __forceinline__ float2 bc2(float s) { return make_float2(s, s); }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    const float2 t = __fmul2_rn(bc2(a.y), make_float2(b.y, b.x));                  // (ay by, ay bx)
+    return __ffma2_rn(bc2(a.x), b, make_float2(-t.x, t.y));
+}
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) {
+    const float2 t = __fmul2_rn(make_float2(a.y, a.x), bc2(b.y));                  // (ay by, ax by)
+    return __ffma2_rn(a, bc2(b.x), make_float2(t.x, -t.y));
+}
+__device__ __forceinline__ float2 cadd_i(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.y, b.x)); }
+__device__ __forceinline__ float2 cadd_i_conj(float2 a, float2 b) {
+    return __fadd2_rn(make_float2(a.x, -a.y), make_float2(b.y, b.x));
+}
+__device__ __forceinline__ float2 cmul_elem(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 cscale(float c, float2 t) { return __fmul2_rn(bc2(c), t); }
+__device__ __forceinline__ float2 caxpy(float c, float2 t, float2 a) { return __ffma2_rn(bc2(c), t, a); }
 
 // v * e^{+2 pi i NUM/DEN}, DEN | 480
 template <int NUM, int DEN, class V>
@@ -90,7 +127,12 @@ __device__ __forceinline__ V mul_root(V v) {
     else if constexpr (k == 3 * QN / 4) return mk2(v.y, -v.x);
     else {
         constexpr F c = (F)cosq(k), s = (F)sinq(k);
-        return mk2(fmad(c, v.x, -(s * v.y)), fmad(c, v.y, s * v.x));
+        if constexpr (sizeof(F) == 4) {
+            const float2 t = __fmul2_rn(bc2(s), make_float2(v.y, v.x));            // (s vy, s vx)
+            return __ffma2_rn(bc2(c), v, make_float2(-t.x, t.y));
+        } else {
+            return mk2(fmad(c, v.x, -(s * v.y)), fmad(c, v.y, s * v.x));
+        }
     }
 }
 
@@ -138,9 +180,9 @@ struct Dft<3> {
     static __device__ __forceinline__ void run(V (&v)[3]) {
         typedef real_t<V> F;
         const V t = cadd(v[1], v[2]), d = csub(v[1], v[2]);
-        const V m = mk2(fmad((F)-0.5, t.x, v[0].x), fmad((F)-0.5, t.y, v[0].y));
+        const V m = caxpy((F)-0.5, t, v[0]);
         constexpr F s = (F)sinq(QN / 3);   // sin 120 deg
-        const V ie = mk2(-s * d.y, s * d.x);          // i * s * d
+        const V ie = cscale(s, cmul_i(d));            // i * s * d
         v[0] = cadd(v[0], t);
         v[1] = cadd(m, ie);
         v[2] = csub(m, ie);
@@ -153,11 +195,11 @@ struct Dft<5> {
         typedef real_t<V> F;
         constexpr F c1 = (F)cosq(QN / 5), c2 = (F)cosq(2 * QN / 5), s1 = (F)sinq(QN / 5), s2 = (F)sinq(2 * QN / 5);
         const V t1 = cadd(v[1], v[4]), t2 = cadd(v[2], v[3]), t3 = csub(v[1], v[4]), t4 = csub(v[2], v[3]);
-        const V m1 = mk2(fmad(c2, t2.x, fmad(c1, t1.x, v[0].x)), fmad(c2, t2.y, fmad(c1, t1.y, v[0].y)));
-        const V m2 = mk2(fmad(c1, t2.x, fmad(c2, t1.x, v[0].x)), fmad(c1, t2.y, fmad(c2, t1.y, v[0].y)));
-        const V a1 = mk2(fmad(s2, t4.x, s1 * t3.x), fmad(s2, t4.y, s1 * t3.y));       // s1 t3 + s2 t4
-        const V a2 = mk2(fmad(-s1, t4.x, s2 * t3.x), fmad(-s1, t4.y, s2 * t3.y));     // s2 t3 - s1 t4
-        const V n1 = mk2(-a1.y, a1.x), n2 = mk2(-a2.y, a2.x);                         // times i
+        const V m1 = caxpy(c2, t2, caxpy(c1, t1, v[0]));
+        const V m2 = caxpy(c1, t2, caxpy(c2, t1, v[0]));
+        const V a1 = caxpy(s2, t4, cscale(s1, t3));        // s1 t3 + s2 t4
+        const V a2 = caxpy(-s1, t4, cscale(s2, t3));       // s2 t3 - s1 t4
+        const V n1 = cmul_i(a1), n2 = cmul_i(a2);          // times i
         v[0] = cadd(v[0], cadd(t1, t2));
         v[1] = cadd(m1, n1);
         v[4] = csub(m1, n1);
@@ -170,7 +212,7 @@ struct Dft<4> {
     template <class V>
     static __device__ __forceinline__ void run(V (&v)[4]) {
         const V a = cadd(v[0], v[2]), b = csub(v[0], v[2]), c = cadd(v[1], v[3]), d = csub(v[1], v[3]);
-        const V id = mk2(-d.y, d.x);
+        const V id = cmul_i(d);
         v[0] = cadd(a, c);
         v[2] = csub(a, c);
         v[1] = cadd(b, id);

@@ -232,9 +232,11 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
         const V* base = sm + S::pad(f0);
 #pragma unroll
         for (int k = 0; k < S::R1; ++k) {
-            const V v = base[k * (S::M1 + S::R2)];
             // a non-finite or zero-energy rider has scale 0: its samples must not turn 0 * inf into NaN for the other rider
-            z[k] = mk2(rsa != (F)0 ? v.x * rsa : (F)0, rsb != (F)0 ? -(v.y * rsb) : (F)0);
+            V v = cmul_elem(base[k * (S::M1 + S::R2)], mk2(rsa, -rsb));
+            if (rsa == (F)0) v.x = (F)0;
+            if (rsb == (F)0) v.y = (F)0;
+            z[k] = v;
         }
         pass1_table<S>(z, f0, sm, tw);
     }
@@ -268,8 +270,8 @@ __global__ void __launch_bounds__(T, MINB) xf_spectra_kernel(XfArgs g) {
         if (f > S::L / 2) continue;
         const V yf = sm[S::pos(f)];
         const V ym = sm[S::pos(f == 0 ? 0 : S::L - f)];
-        Xa[f] = mk2(half * (yf.x + ym.x), half * (ym.y - yf.y));
-        if (has_b) Xb[f] = mk2(-half * (yf.y + ym.y), -half * (yf.x - ym.x));
+        Xa[f] = cscale(half, cadd(mk2(yf.x, -yf.y), ym));
+        if (has_b) Xb[f] = cscale(-half, cadd(mk2(yf.y, yf.x), mk2(ym.y, -ym.x)));
     }
 }
 
@@ -365,9 +367,9 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     // Z[f] for any f in [0, L): Z = a + i b on the stored half, conj(a) + i conj(b) on the mirrored one
     auto fetch = [&](int f) -> V {
         V a, b;
-        if (f <= L / 2) { cross(f, a, b); return mk2(a.x - b.y, a.y + b.x); }
+        if (f <= L / 2) { cross(f, a, b); return cadd_i(a, b); }
         cross(L - f, a, b);
-        return mk2(a.x + b.y, b.x - a.y);
+        return cadd_i_conj(a, b);
     };
 
     if constexpr (SCREEN) {
@@ -380,8 +382,8 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             const V yj = has1 ? ldg2(Xj1 + f) : mk2((F)0, (F)0);
             const V yi = same_i ? xi : ldg2(Xi1 + f);
             const V a = cmulc(xi, xj), b = cmulc(yi, yj);
-            sm[S::pad(f)] = mk2(a.x - b.y, a.y + b.x);                    // Z[f]   = a + i b
-            if (f != 0 && f != L / 2) sm[S::pad(L - f)] = mk2(a.x + b.y, b.x - a.y);   // Z[L-f] = conj(a) + i conj(b)
+            sm[S::pad(f)] = cadd_i(a, b);                    // Z[f]   = a + i b
+            if (f != 0 && f != L / 2) sm[S::pad(L - f)] = cadd_i_conj(a, b);   // Z[L-f] = conj(a) + i conj(b)
         }
         __syncthreads();
         for (int f0 = tid; f0 < M1; f0 += T) {
@@ -442,8 +444,8 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             for (int k = 0; k < R1; ++k) {
                 const bool direct = k < HALF;
                 const V a = cmulc(vi0[k], vj0[k]), b = cmulc(vi1[k], vj1[k]);
-                const V zg = mk2(a.x - b.y, a.y + b.x);     // Z[g]
-                const V zm = mk2(a.x + b.y, b.x - a.y);     // Z[L-g]
+                const V zg = cadd_i(a, b);     // Z[g]
+                const V zm = cadd_i_conj(a, b);     // Z[L-g]
                 zA[k] = direct ? zg : zm;
                 zB[(R1 - k) % R1] = direct ? zm : zg;      // slot R1-1-k, rotated by one (see store_pair)
             }
