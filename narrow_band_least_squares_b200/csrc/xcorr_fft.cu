@@ -296,10 +296,15 @@ __device__ __forceinline__ void top_merge(Top& a, double b1, double b2, int l1) 
     }
 }
 __device__ __forceinline__ void pair_channels(int p, int C, int& ci, int& cj) {
-    int i = 0, rem = p;            // i<j row-major (lts_classes.py:840)
-    while (rem >= C - 1 - i) { rem -= C - 1 - i; ++i; }
+    // i<j row-major (lts_classes.py:840): row i starts at s(i) = i (2C - i - 1) / 2.  Closed form through the root of
+    // s(i) = p in FP32 (exact integers below 2^24), then at most one step either way
+    const float b = (float)(2 * C - 1);
+    int i = (int)((b - sqrtf(fmaxf(b * b - 8.0f * (float)p, 0.0f))) * 0.5f);
+    i = max(0, min(i, C - 2));
+    if (i * (2 * C - i - 1) / 2 > p) --i;
+    else if (i + 1 <= C - 2 && (i + 1) * (2 * C - i - 2) / 2 <= p) ++i;
     ci = i;
-    cj = i + 1 + rem;
+    cj = i + 1 + p - i * (2 * C - i - 1) / 2;
 }
 __device__ __forceinline__ int pair_index(int ci, int cj, int C) { return ci * (2 * C - ci - 1) / 2 + (cj - ci - 1); }
 
@@ -350,7 +355,10 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
     }
     int i0, j0, i1, j1;
     pair_channels(p0, g.C, i0, j0);
-    pair_channels(p1, g.C, i1, j1);
+    if (g.items) pair_channels(p1, g.C, i1, j1);
+    else if (!has1) { i1 = i0; j1 = j0; }
+    else if (j0 + 1 < g.C) { i1 = i0; j1 = j0 + 1; }      // p1 = p0 + 1: the next pair of the same row, or the first of the next
+    else { i1 = i0 + 1; j1 = i0 + 2; }
     const V* sbase0 = static_cast<const V*>(g.spec) + (int64_t)wl0 * g.C * g.SP;
     const V* sbase1 = static_cast<const V*>(g.spec) + (int64_t)wl1 * g.C * g.SP;
     const V *Xi0 = sbase0 + (int64_t)i0 * g.SP, *Xj0 = sbase0 + (int64_t)j0 * g.SP;
@@ -376,14 +384,35 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         // ---- FP32: cross-spectra straight into shared memory (natural order; every load independent, so the L2
         // latency is hidden by memory-level parallelism), then a plain in-place radix-R1 pass.  Register use stays
         // low enough for 24 warps per SM. ----
+        // A CTA without a second rider carries its first one twice (p1 = p0 above), so the loop has no rider test; f and
+        // L - f advance by T per step, hence pad() of both by the constant PSTEP: two base addresses, immediate offsets.
+        // Thread 0's first mirror store (f = 0, "Z[L]") lands in the spare slot behind the array; f = L/2 has no mirror
+        // and is done by one thread after the loop.
+        static_assert((L / 2) % T == 0 && T % S::R3 == 0, "load loop: whole steps, constant pad() stride");
+        constexpr int NK = L / 2 / T, PSTEP = T + T / S::R3;
+        V* pf = sm + S::pad(tid);
+        V* pm = sm + S::pad(L - tid);
+        const V *gi0 = Xi0 + tid, *gj0 = Xj0 + tid, *gi1 = Xi1 + tid, *gj1 = Xj1 + tid;
+        if (same_i) {
 #pragma unroll 4
-        for (int f = tid; f <= L / 2; f += T) {
-            const V xi = ldg2(Xi0 + f), xj = ldg2(Xj0 + f);
-            const V yj = has1 ? ldg2(Xj1 + f) : mk2((F)0, (F)0);
-            const V yi = same_i ? xi : ldg2(Xi1 + f);
-            const V a = cmulc(xi, xj), b = cmulc(yi, yj);
-            sm[S::pad(f)] = cadd_i(a, b);                    // Z[f]   = a + i b
-            if (f != 0 && f != L / 2) sm[S::pad(L - f)] = cadd_i_conj(a, b);   // Z[L-f] = conj(a) + i conj(b)
+            for (int k = 0; k < NK; ++k) {
+                const V xi = ldg2(gi0 + k * T), xj = ldg2(gj0 + k * T), yj = ldg2(gj1 + k * T);
+                const V a = cmulc(xi, xj), b = cmulc(xi, yj);
+                pf[k * PSTEP] = cadd_i(a, b);                    // Z[f]   = a + i b
+                pm[-k * PSTEP] = cadd_i_conj(a, b);              // Z[L-f] = conj(a) + i conj(b)
+            }
+        } else {
+#pragma unroll 4
+            for (int k = 0; k < NK; ++k) {
+                const V xi = ldg2(gi0 + k * T), xj = ldg2(gj0 + k * T), yi = ldg2(gi1 + k * T), yj = ldg2(gj1 + k * T);
+                const V a = cmulc(xi, xj), b = cmulc(yi, yj);
+                pf[k * PSTEP] = cadd_i(a, b);
+                pm[-k * PSTEP] = cadd_i_conj(a, b);
+            }
+        }
+        if (tid == 0) {
+            const V a = cmulc(ldg2(Xi0 + L / 2), ldg2(Xj0 + L / 2)), b = cmulc(ldg2(Xi1 + L / 2), ldg2(Xj1 + L / 2));
+            sm[S::pad(L / 2)] = cadd_i(a, b);
         }
         __syncthreads();
         for (int f0 = tid; f0 < M1; f0 += T) {
@@ -1093,7 +1122,7 @@ static XfPlan make_plan() {
     XfPlan p;
     p.L = S::L;
     p.threads = T;
-    p.smem = (size_t)S::SMEM_ELEMS * sizeof(V);
+    p.smem = (size_t)(S::SMEM_ELEMS + 2) * sizeof(V);     // + the spare slot of the pair kernel's load loop (kept 16-byte sized)
     p.spectra = xf_spectra_kernel<S, T, MINB, V>;
     p.pair = xf_pair_kernel<S, T, MINB, V>;
     return p;
