@@ -255,6 +255,16 @@ def parity_block(eng, j, rec, ref_out, port_out, args, method):
     P, nb = plan.npairs, plan.nbands
     out = {"sample": f"{rec.npts / j['fs'] / 60.0:g}-minute slice of the workload (the cpu_baseline record), all {nb} bands",
            "estimates": int(plan.nwin), "pair_windows": int(plan.nwin) * P}
+    # the timed steps ask for no per-pair cmax (lazy verification, NBLS_OPT_LAZY_VERIFY); the comparison below runs WITH
+    # cmax (every pair-window evaluated in FP64).  Both paths must agree: lags and estimates bit for bit, MdCCM to the last bit
+    fast = eng.run(plan, rec.data, Results(plan, pinned=False, want_cmax=False))
+    with np.errstate(invalid="ignore"):
+        out["timed_path_vs_cmax_path"] = {
+            "lag_mismatches": int((fast.lag != res.lag).sum()),
+            "estimates_bit_identical": bool(all(np.array_equal(getattr(fast, k), getattr(res, k), equal_nan=True)
+                                                for k in ("mad", "vel", "baz", "sigma_tau"))),
+            "max_abs_dmdccm": float(np.nanmax(np.abs(fast.mdccm - res.mdccm), initial=0.0)),
+            "lts_flags_equal": (bool(np.array_equal(fast.weights, res.weights)) if res.weights is not None else None)}
     if port_out is not None and args.max_lag < 0:
         mism, mism_filt, nan_ok, dvel, dbaz, dmd, dsig, dcmax, flag_mism = 0, None, True, 0.0, 0.0, 0.0, 0.0, 0.0, 0
         for b in range(nb):

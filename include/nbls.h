@@ -227,6 +227,11 @@ int nbls_memcpy_d2h(nbls_ctx* ctx, void* dst_host, const void* src_dev, size_t b
 #define NBLS_OPT_FILTER_P1_SUB 8     /* sub-chunks per chunk of the forward state pass: 1 (default, also 0), 2, 4 or 8 */
 #define NBLS_OPT_FILTER_OVERLAP 9    /* 1 (default): the filter runs two band groups side by side on two streams (the state
                                         passes of the low bands hide under the output passes of the high bands); 0: one stream */
+#define NBLS_OPT_LAZY_VERIFY 10      /* 1 (default): when the caller asks for no per-pair cmax (nbls_outputs.cmax = NULL), the FP32-screen
+                                        path evaluates in FP64 only the pair-windows whose result needs it: those with more
+                                        than one candidate lag, and per window the pairs whose screen value lies within the
+                                        screen's error band of the median (MdCCM is the only consumer of cmax then and stays
+                                        exact).  0: every pair-window is evaluated in FP64 */
 #define NBLS_OPT_COUNT 16
 int nbls_set_option(nbls_ctx* ctx, int32_t key, int64_t value);
 int nbls_get_option(nbls_ctx* ctx, int32_t key, int64_t* value);

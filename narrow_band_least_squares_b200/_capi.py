@@ -23,7 +23,7 @@ c_uint8_p = C.POINTER(C.c_uint8)
 XCORR_AUTO, XCORR_DIRECT, XCORR_FFT, XCORR_FFT32 = 0, 1, 2, 3
 # nbls_set_option keys (include/nbls.h)
 (OPT_PROFILE, OPT_TWO_STAGE, OPT_FILTER_SPLIT, OPT_FILTER_SHARED_P1, OPT_FILTER_LANES, OPT_LTS_FP64_RANK,
- OPT_SCREEN_AUDIT, OPT_FILTER_P1_WARPS, OPT_FILTER_P1_SUB, OPT_FILTER_OVERLAP) = range(10)
+ OPT_SCREEN_AUDIT, OPT_FILTER_P1_WARPS, OPT_FILTER_P1_SUB, OPT_FILTER_OVERLAP, OPT_LAZY_VERIFY) = range(11)
 
 
 class FilterDesc(C.Structure):

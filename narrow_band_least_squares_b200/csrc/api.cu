@@ -288,6 +288,7 @@ int nbls_create(nbls_ctx** out, int32_t device) {
     ctx->opt[NBLS_OPT_FILTER_SHARED_P1] = 1;
     ctx->opt[NBLS_OPT_FILTER_LANES] = 131072;
     ctx->opt[NBLS_OPT_FILTER_OVERLAP] = 1;
+    ctx->opt[NBLS_OPT_LAZY_VERIFY] = 1;
     *out = ctx;
     return NBLS_OK;
 }
@@ -298,7 +299,7 @@ int nbls_destroy(nbls_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->coef, &ctx->state, &ctx->carry, &ctx->taper, &ctx->filt, &ctx->geom, &ctx->lts_tab,
                       &ctx->xin, &ctx->res, &ctx->lagbuf, &ctx->cmaxbuf, &ctx->wbuf, &ctx->scratch, &ctx->spec,
-                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat, &ctx->wfail, &ctx->audit};
+                      &ctx->energy, &ctx->flags, &ctx->cand, &ctx->sval, &ctx->xstat, &ctx->wfail, &ctx->audit, &ctx->lazy};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     for (auto& kv : ctx->fft_tw)
@@ -501,7 +502,10 @@ int nbls_run_device(nbls_ctx* ctx, const nbls_job* job, const double* x_dev, int
     NBLS_CHECK(count_windows(job, nchan, round_up(npts, 16), &E));
     NBLS_CHECK(record(ctx, EV_START));
     NBLS_CHECK(record(ctx, EV_H2D));
-    NBLS_CHECK(run_device_inner(ctx, job, x_dev, nchan, npts, ldx, out_dev, E));
+    ctx->cmax_median_only = out_dev->cmax == nullptr;
+    const int rc_run = run_device_inner(ctx, job, x_dev, nchan, npts, ldx, out_dev, E);
+    ctx->cmax_median_only = false;
+    NBLS_CHECK(rc_run);
     NBLS_CHECK(record(ctx, EV_D2H));
     ctx->ev_valid = true;
     return NBLS_OK;
@@ -536,7 +540,10 @@ int nbls_run_host(nbls_ctx* ctx, const nbls_job* job, const double* x_host, int3
     NBLS_CUDA(cudaMemcpy2DAsync(ctx->xin.p, (size_t)ld * sizeof(double), x_host, (size_t)ldx_host * sizeof(double),
                                 (size_t)npts * sizeof(double), C, cudaMemcpyHostToDevice, ctx->stream));
     NBLS_CHECK(record(ctx, EV_H2D));
-    NBLS_CHECK(run_device_inner(ctx, job, (const double*)ctx->xin.p, C, npts, ld, &od, E));
+    ctx->cmax_median_only = oh->cmax == nullptr;
+    const int rc_run = run_device_inner(ctx, job, (const double*)ctx->xin.p, C, npts, ld, &od, E);
+    ctx->cmax_median_only = false;
+    NBLS_CHECK(rc_run);
     if (E > 0) {
         auto back = [&](void* dst, const void* src, size_t bytes) -> int {
             if (dst) NBLS_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, ctx->stream));

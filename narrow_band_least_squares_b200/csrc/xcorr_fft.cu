@@ -40,6 +40,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "stats.cuh"
 #include "fft_radix.cuh"
 
 namespace nbls {
@@ -48,6 +49,7 @@ using namespace fft;
 
 constexpr double XF_TAU = 1e-10;   // FP64 FFT: near-tie threshold, normalised correlation units
 constexpr float XF_TAU32 = 2e-5f;  // FP32 screen: candidate band below the FP32 maximum (error seen: <= 4e-7)
+constexpr double XF_EPS32 = 0.5 * 2e-5;   // = XF_TAU32 / 2: the error of one FP32 screen value the candidate band allows for
 constexpr int XF_KC = 4;           // candidate lags kept per pair-window (more -> time-domain kernel)
 
 struct XfArgs {
@@ -89,6 +91,15 @@ struct XfArgs {
     // pair-window with wl < dump_wn - [dump_wn * P][L] reals of the transform's precision, unnormalised (value * L)
     void* dump;
     int dump_wn;
+    // lazy verification (NBLS_OPT_LAZY_VERIFY, FP32 screen, per-pair cmax not requested): a pair-window with ONE candidate
+    // keeps the screen's lag and value (apx = 1); only the others (need_list) are evaluated in FP64, plus, per window, the
+    // pairs whose value decides the median (xf_median_select_kernel).  The screen's values are taken to be within XF_EPS32
+    // of the exact ones - the same premise the candidate band rests on.
+    int lazy;
+    unsigned char* apx;   // [wb*P] 1 = cmax of batch item wl*P+p is the FP32 screen value
+    int* need_list;       // [wb*P] batch items to evaluate exactly (any order: items are independent)
+    int* need_count;
+    const int* items_count;   // item mode of xf_verify_items_kernel: number of items on the device (else n_items)
 };
 
 __device__ __forceinline__ int win_index(const XfArgs& g, int s) { return g.wlist ? g.wlist[s] : g.w0 + s; }
@@ -614,7 +625,27 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
                     if (cl[j_] < cl[j_ - 1]) { const int t_ = cl[j_]; cl[j_] = cl[j_ - 1]; cl[j_ - 1] = t_; }
 #pragma unroll
             for (int s_ = 0; s_ < XF_KC; ++s_) cd[s_] = cl[s_] == INT_MAX ? INT_MIN : cl[s_];
-            g.sval[loc] = (tid == 0 ? mr : mi) / (float)L;
+            const float sv = (tid == 0 ? mr : mi) / (float)L;
+            g.sval[loc] = sv;
+            if (g.lazy) {
+                bool approx = false;
+                if (give && cnt == 1) {
+                    // one lag inside the candidate band: it is the arg-max; its value is known to XF_EPS32
+                    approx = true;
+                    g.lag[item] = cl[0];
+                    if (g.cmax) g.cmax[item] = (double)sv;
+                    if (g.k0 >= 0) {
+                        // stage-A proof (see xf_verify_kernel) on the screen value less its error, in normalised units
+                        const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
+                        const double* pj = g.part + ((int64_t)wl * g.C + cj) * 2;
+                        const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
+                        if (!(((double)sv - XF_EPS32) * den > sqrt(b2) * (1.0 + 1e-12))) g.pf_flag[loc] = 1;
+                    }
+                } else if (give) {
+                    g.need_list[atomicAdd(g.need_count, 1)] = (int)loc;
+                }
+                g.apx[loc] = approx ? 1 : 0;
+            }
         }
     } else {
     // ---- pass 3 + arg-max straight from registers ----
@@ -946,65 +977,131 @@ __global__ void __launch_bounds__(XV_SL * 32) xf_verify_items_kernel(XfArgs g) {
     __shared__ double sp[XV_SL], se[XF_KC - 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int N = g.N;
-    const int it = g.items[blockIdx.x];
-    const int wl = it / g.P, p = it - wl * g.P;
-    const int32_t* cd = g.cand + (int64_t)it * XF_KC;
-    if (cd[0] == INT_MIN) return;            // dead pair or handed to the time-domain kernel by the pair kernel
-    int ci, j;
-    pair_channels(p, g.C, ci, j);
-    const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
-    {
-        const double* src = g.y + (int64_t)ci * g.ldy + t0;
+    // the list length is a launch argument (grid = items) or sits on the device (any grid; CTAs stride over the list)
+    const int n_list = g.items_count ? *g.items_count : g.n_items;
+    for (int e = blockIdx.x; e < n_list; e += gridDim.x) {
+        const int it = g.items[e];
+        const int wl = it / g.P, p = it - wl * g.P;
+        const int32_t* cd = g.cand + (int64_t)it * XF_KC;
+        if (cd[0] == INT_MIN) continue;          // dead pair or handed to the time-domain kernel by the pair kernel
+        int ci, j;
+        pair_channels(p, g.C, ci, j);
+        const int64_t t0 = g.first + (int64_t)(g.w0 + wl) * g.hop;
+        {
+            const double* src = g.y + (int64_t)ci * g.ldy + t0;
 #pragma unroll 8
-        for (int n = tid; n < N; n += XV_SL * 32) xs[n] = __ldg(src + n);
-    }
-    __syncthreads();
-    const double* xj = g.y + (int64_t)j * g.ldy + t0;
-    {
-        const int SLN = ((N + XV_SL - 1) / XV_SL + 31) / 32 * 32;
-        const int a = min(N, warp * SLN), b = min(N, a + SLN);
-        const int k[1] = {cd[0]}, off[1] = {cd[0]};
-        double acc[1] = {0.0};
-        verify_slice<1, true>(xj, xs, off, k, a, b, N, lane, acc);
+            for (int n = tid; n < N; n += XV_SL * 32) xs[n] = __ldg(src + n);
+        }
+        __syncthreads();
+        const double* xj = g.y + (int64_t)j * g.ldy + t0;
+        {
+            const int SLN = ((N + XV_SL - 1) / XV_SL + 31) / 32 * 32;
+            const int a = min(N, warp * SLN), b = min(N, a + SLN);
+            const int k[1] = {cd[0]}, off[1] = {cd[0]};
+            double acc[1] = {0.0};
+            verify_slice<1, true>(xj, xs, off, k, a, b, N, lane, acc);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], o);
-        if (lane == 0) sp[warp] = acc[0];
-    }
-    if (warp + 1 < XF_KC && cd[warp + 1] != INT_MIN) {
-        const int ks = cd[warp + 1];
-        const int nlo = max(0, -ks), nhi = min(N, N - ks);
-        double d = 0.0;
+            for (int o = 16; o > 0; o >>= 1) acc[0] += __shfl_xor_sync(0xffffffffu, acc[0], o);
+            if (lane == 0) sp[warp] = acc[0];
+        }
+        if (warp + 1 < XF_KC && cd[warp + 1] != INT_MIN) {
+            const int ks = cd[warp + 1];
+            const int nlo = max(0, -ks), nhi = min(N, N - ks);
+            double d = 0.0;
 #pragma unroll 4
-        for (int n = nlo + lane; n < nhi; n += 32) d = fma(xs[ks + n], __ldg(xj + n), d);
+            for (int n = nlo + lane; n < nhi; n += 32) d = fma(xs[ks + n], __ldg(xj + n), d);
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
-        if (lane == 0) se[warp] = d;
-    }
-    __syncthreads();
-    if (tid != 0) return;
-    double best = 0.0;
+            for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+            if (lane == 0) se[warp] = d;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double best = 0.0;
 #pragma unroll
-    for (int sl = 0; sl < XV_SL; ++sl) best += sp[sl];
-    int bl = cd[0];
-    unsigned long long ncand = 1;
-    for (int s_ = 1; s_ < XF_KC && cd[s_] != INT_MIN; ++s_) {
-        const double d = se[s_ - 1];
-        const int ks = cd[s_];
-        if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
-        ++ncand;
+            for (int sl = 0; sl < XV_SL; ++sl) best += sp[sl];
+            int bl = cd[0];
+            unsigned long long ncand = 1;
+            for (int s_ = 1; s_ < XF_KC && cd[s_] != INT_MIN; ++s_) {
+                const double d = se[s_ - 1];
+                const int ks = cd[s_];
+                if (d > best || (d == best && ks < bl)) { best = d; bl = ks; }
+                ++ncand;
+            }
+            const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
+            const double c = best / sqrt(Ei * Ej);
+            const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
+            g.lag[item] = bl;
+            if (g.cmax) g.cmax[item] = c;
+            if (g.apx) g.apx[it] = 0;
+            if (g.k0 >= 0) {      // stage-A proof, as in xf_verify_kernel
+                const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
+                const double* pj = g.part + ((int64_t)wl * g.C + j) * 2;
+                const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
+                if (!(best > sqrt(b2) * (1.0 + 1e-12))) g.pf_flag[it] = 1;
+            }
+            atomicAdd(g.stat, ncand);
+            const float ee = fabsf((float)(c - (double)g.sval[it]));
+            if (!(ee <= 0.25f * XF_TAU32)) {
+                g.flag_list[atomicAdd(g.flag_count, 1)] = (int)item;
+                atomicAdd(g.stat + 1, 1ULL);
+            } else {
+                atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(ee));
+            }
+        }
+        __syncthreads();      // xs, sp and se are reused by the next item
     }
-    const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + j];
-    const double c = best / sqrt(Ei * Ej);
-    const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
-    g.lag[item] = bl;
-    if (g.cmax) g.cmax[item] = c;
-    atomicAdd(g.stat, ncand);
-    const float ee = fabsf((float)(c - (double)g.sval[it]));
-    if (!(ee <= 0.25f * XF_TAU32)) {
-        g.flag_list[atomicAdd(g.flag_count, 1)] = (int)item;
-        atomicAdd(g.stat + 1, 1ULL);
-    } else {
-        atomicMax(g.stat + 2, (unsigned long long)__float_as_uint(ee));
+}
+
+// Lazy verification, last step: per window, which pairs still carry a screen value (apx) that could be one of the middle
+// order statistics of cmax?  v_p = stored values, each within XF_EPS32 of the exact e_p; m = a middle order statistic of v.
+// The same order statistic m* of e lies within XF_EPS32 of m, and a pair with |v_p - m| > 2 XF_EPS32 is on the same side of
+// m* before and after it is replaced by its exact value.  So once every apx pair within 2 XF_EPS32 of either middle
+// statistic is evaluated exactly, the median of the stored values IS the exact median (numpy nanmedian semantics as in
+// stats.cuh).  One warp per window; the listed pairs go to xf_verify_items_kernel.
+constexpr int XM_WARPS = 4;
+__global__ void __launch_bounds__(XM_WARPS * 32) xf_median_select_kernel(const double* cmax, const unsigned char* apx, int P,
+                                                                        int wn, int* need_list, int* need_count) {
+    extern __shared__ double xm_sm[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double* buf = xm_sm + (size_t)warp * P;
+    for (int w = blockIdx.x * XM_WARPS + warp; w < wn; w += gridDim.x * XM_WARPS) {
+        const double* cm = cmax + (int64_t)w * P;
+        const unsigned char* ap = apx + (int64_t)w * P;
+        int m = 0;
+        for (int base = 0; base < P; base += 32) {
+            const int p = base + lane;
+            const double v = p < P ? cm[p] : qnan();
+            const bool ok = v == v;
+            const unsigned msk = __ballot_sync(0xffffffffu, ok);
+            if (ok) buf[m + __popc(msk & ((1u << lane) - 1u))] = v;
+            m += __popc(msk);
+        }
+        __syncwarp();
+        if (m > 0) {
+            const int r_hi = m >> 1, r_lo = (m & 1) ? r_hi : r_hi - 1;
+            double lo = 0.0, hi = 0.0;
+            bool have_lo = false, have_hi = false;
+            for (int p = lane; p < m; p += 32) {
+                const double v = buf[p];
+                int rank = 0;
+                for (int q = 0; q < m; ++q) {
+                    const double u = buf[q];
+                    rank += (u < v) || (u == v && q < p);
+                }
+                if (rank == r_lo) { lo = v; have_lo = true; }
+                if (rank == r_hi) { hi = v; have_hi = true; }
+            }
+            const unsigned mlo = __ballot_sync(0xffffffffu, have_lo), mhi = __ballot_sync(0xffffffffu, have_hi);
+            lo = __shfl_sync(0xffffffffu, lo, __ffs(mlo) - 1);
+            hi = __shfl_sync(0xffffffffu, hi, __ffs(mhi) - 1);
+            const double band = 2.0 * XF_EPS32 * (1.0 + 1e-9);
+            for (int p = lane; p < P; p += 32) {
+                if (!ap[p]) continue;
+                const double v = cm[p];
+                if (fabs(v - lo) <= band || fabs(v - hi) <= band) need_list[atomicAdd(need_count, 1)] = w * P + p;
+            }
+        }
+        __syncwarp();
     }
 }
 
@@ -1280,9 +1377,23 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         NBLS_CUDA(cudaFuncSetAttribute(q->pair, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)q->smem));
     }
 
+    // lazy verification: only where the caller wants no per-pair cmax (the audit keeps the dense evaluation)
+    const bool lazy = fp32 && ctx->opt[NBLS_OPT_LAZY_VERIFY] != 0 && ctx->opt[NBLS_OPT_SCREEN_AUDIT] == 0 &&
+                      (ctx->cmax_median_only || cmax == nullptr);
+    if (lazy) {
+        NBLS_CHECK(ensure(ctx, ctx->lazy, round_up((size_t)wb * P, 256) + ((size_t)wb * P + 8) * sizeof(int)));
+        NBLS_CUDA(allow_max_dynamic_smem(xf_verify_items_kernel, ctx->smem_optin));
+        NBLS_CUDA(allow_max_dynamic_smem(xf_median_select_kernel, ctx->smem_optin));
+    }
     XfArgs a;
     memset(&a, 0, sizeof(a));
     a.y = yband; a.ldy = ldy; a.C = C; a.P = P; a.N = N; a.hop = hop; a.first = first;
+    a.lazy = lazy ? 1 : 0;
+    if (lazy) {
+        a.apx = (unsigned char*)ctx->lazy.p;
+        a.need_count = (int*)((char*)ctx->lazy.p + round_up((size_t)wb * P, 256));
+        a.need_list = a.need_count + 8;
+    }
     a.spec = ctx->spec.p;
     a.energy = (double*)ctx->energy.p;
     a.part = a.energy + (size_t)wb * C;
@@ -1344,8 +1455,19 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         ctx->launches += 3;
         return NBLS_OK;
     };
+    // lazy mode: exact evaluation of the pair-windows on the need list (length on the device: a fixed grid strides over it)
+    auto verify_needed = [&]() -> int {
+        XfArgs v = a;
+        v.items = a.need_list; v.items_count = a.need_count; v.n_items = 0; v.wlist = nullptr;
+        KernelGroupScope ks(ctx, KG_VERIFY_ITEMS, 0.0);
+        xf_verify_items_kernel<<<(unsigned)(ctx->sm_count * 8), XV_SL * 32, (size_t)N * sizeof(double), ctx->stream>>>(v);
+        NBLS_CUDA(cudaGetLastError());
+        ctx->launches += 1;
+        return NBLS_OK;
+    };
     auto pass = [&](const XfPlan* q) -> int {
         NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
+        if (lazy) NBLS_CUDA(cudaMemsetAsync(a.need_count, 0, sizeof(int), ctx->stream));
         int wa = 0;
         a.dump = nullptr; a.dump_wn = 0;
         if (audit) {
@@ -1365,7 +1487,9 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         }
         NBLS_CUDA(cudaGetLastError());
         ctx->launches += 2;
-        if (fp32) {
+        if (lazy) {
+            NBLS_CHECK(verify_needed());
+        } else if (fp32) {
             const int nib = (C - 1 + ib - 1) / ib;
             KernelGroupScope ks(ctx, KG_VERIFY, (double)a.wn * P * 2.0 * N);
             verify<<<(unsigned)(a.wn * nib), vnw * 32, vsmem, ctx->stream>>>(a);
@@ -1376,6 +1500,23 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         a.dump = nullptr; a.dump_wn = 0;
         return settle();
     };
+    // lazy mode, end of a batch: the pairs that decide the median of a window get their exact value
+    auto median_step = [&](int w0, int wn) -> int {
+        if (!lazy || !cmax) return NBLS_OK;
+        NBLS_CUDA(cudaMemsetAsync(a.flag_count, 0, sizeof(int), ctx->stream));
+        NBLS_CUDA(cudaMemsetAsync(a.need_count, 0, sizeof(int), ctx->stream));
+        a.w0 = w0; a.wn = wn; a.wlist = nullptr; a.items = nullptr; a.n_items = 0; a.k0 = -1; a.lag_max = lag_full;
+        {
+            KernelGroupScope ks(ctx, KG_VERIFY_ITEMS, 0.0);
+            const int grid = std::min((wn + XM_WARPS - 1) / XM_WARPS, ctx->sm_count * 16);
+            xf_median_select_kernel<<<grid, XM_WARPS * 32, (size_t)XM_WARPS * P * sizeof(double), ctx->stream>>>(
+                cmax + (int64_t)w0 * P, a.apx, P, wn, a.need_list, a.need_count);
+            NBLS_CUDA(cudaGetLastError());
+            ctx->launches += 1;
+        }
+        NBLS_CHECK(verify_needed());
+        return settle();
+    };
     int64_t n_redo = 0, n_redo_pairs = 0;
     for (int w0 = 0; w0 < W; w0 += wb) {
         const int wn = std::min(wb, W - w0);
@@ -1384,6 +1525,7 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
             a.k0 = -1; a.lag_max = lag_full;
             a.SP = SP; a.tw = tw;
             NBLS_CHECK(pass(pl));
+            NBLS_CHECK(median_step(w0, wn));
             continue;
         }
         // stage A: |lag| <= k0 with the shorter transform, plus the proof per pair-window that nothing beyond k0 can win
@@ -1403,7 +1545,10 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         NBLS_CUDA(cudaMemcpyAsync(hcount, a.pf_count, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         NBLS_CUDA(cudaStreamSynchronize(ctx->stream));
         const int nfail = hcount[0], nwin_fail = hcount[1];
-        if (nfail == 0) continue;
+        if (nfail == 0) {
+            NBLS_CHECK(median_step(w0, wn));
+            continue;
+        }
         n_redo += nwin_fail;
         n_redo_pairs += nfail;
         a.k0 = -1; a.lag_max = lag_full;
@@ -1416,18 +1561,24 @@ int xcorr_fft_band(nbls_ctx* ctx, const double* yband, int64_t ldy, int C, int N
         }
         NBLS_CUDA(cudaGetLastError());
         a.wlist = nullptr; a.items = a.pf_list; a.n_items = nfail;
+        if (lazy) NBLS_CUDA(cudaMemsetAsync(a.need_count, 0, sizeof(int), ctx->stream));
         {
             KernelGroupScope ks(ctx, KG_PAIR, (double)((nfail + 1) / 2) * (fft_flop(pl) + 16.0 * pl->L));
             pl->pair<<<(unsigned)((nfail + 1) / 2), pl->threads, pl->smem, ctx->stream>>>(a);
         }
         NBLS_CUDA(cudaGetLastError());
-        {
+        if (lazy) {
+            a.items = nullptr; a.n_items = 0;
+            NBLS_CHECK(verify_needed());
+        } else {
             KernelGroupScope ks(ctx, KG_VERIFY_ITEMS, (double)nfail * 2.0 * N);
             xf_verify_items_kernel<<<(unsigned)nfail, XV_SL * 32, (size_t)N * sizeof(double), ctx->stream>>>(a);
+            NBLS_CUDA(cudaGetLastError());
+            ctx->launches += 1;
         }
-        NBLS_CUDA(cudaGetLastError());
-        ctx->launches += 3;
+        ctx->launches += 2;
         NBLS_CHECK(settle());
+        NBLS_CHECK(median_step(w0, wn));
     }
     if (pa) {
         ctx->ts_windows += W;

@@ -201,6 +201,53 @@ def test_screen_audit_on_plane_wave_bands(eng):
 
 
 # ---------------------------------------------------------------------------------------------
+# lazy verification (NBLS_OPT_LAZY_VERIFY): without a per-pair cmax request only the pair-windows that need it are
+# evaluated in FP64 - the lags must not change by a bit, the MdCCM by no more than the last one
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,hours,noise", [("c3", 0.25, False), ("c3", 0.2, True), ("c2", 0.5, False), ("c1", None, False)],
+                         ids=["c3_plane_wave", "c3_noise", "c2_lts", "c1"])
+def test_lazy_verification_changes_nothing(eng, name, hours, noise):
+    from narrow_band_least_squares_b200.configs import config_plan
+    from narrow_band_least_squares_b200.engine import Results
+    from narrow_band_least_squares_b200.synth import config_record
+    rec = config_record(name, hours=hours)
+    data = rec.data
+    if noise:
+        data = np.random.default_rng(77).standard_normal(data.shape)      # incoherent: flat cmax distribution, many redone pairs
+    plan = config_plan(name, rec.npts, rec.rij)
+    out = {}
+    for lazy in (1, 0):
+        eng.set_option(_capi.OPT_LAZY_VERIFY, lazy)
+        eng.xcorr_stats(reset=True)
+        try:
+            res = eng.run(plan, data, Results(plan, pinned=False, want_cmax=False))
+        finally:
+            eng.set_option(_capi.OPT_LAZY_VERIFY, 1)
+        st = eng.xcorr_stats(reset=True)
+        out[lazy] = (res, st)
+    full = eng.run(plan, data, Results(plan, pinned=False, want_cmax=True))      # a cmax request: dense evaluation, exact cmax
+    a, b = out[1][0], out[0][0]
+    assert np.array_equal(a.lag, b.lag) and np.array_equal(a.lag, full.lag)
+    for k in ("mad", "vel", "baz", "sigma_tau", "slowness"):
+        assert np.array_equal(getattr(a, k), getattr(b, k), equal_nan=True), k
+        assert np.array_equal(getattr(a, k), getattr(full, k), equal_nan=True), k
+    # MdCCM: the same middle pairs, evaluated exactly; the item kernel and the dense kernel add the same FP64 products in a
+    # different order, hence the last bit (bar for MdCCM: 1e-9)
+    assert np.array_equal(np.isnan(a.mdccm), np.isnan(b.mdccm))
+    assert np.nanmax(np.abs(a.mdccm - b.mdccm), initial=0.0) <= 1e-15
+    assert np.array_equal(b.mdccm, full.mdccm, equal_nan=True)
+    if a.weights is not None:
+        assert np.array_equal(a.weights, b.weights)
+    # the MdCCM really is the median of the exact per-pair maxima
+    assert np.allclose(a.mdccm, np.nanmedian(full.cmax, axis=1), rtol=0, atol=1e-15, equal_nan=True)
+    # and the lazy run evaluated far fewer candidates exactly
+    va, vb = out[1][1]["verified"], out[0][1]["verified"]
+    assert 0 < va < vb, (va, vb)
+    if not noise and name == "c3":
+        assert va < 0.35 * vb, (va, vb)
+
+
+# ---------------------------------------------------------------------------------------------
 # config 5: a batch of independent arrays, OLS + LTS sweep (batch.py)
 # ---------------------------------------------------------------------------------------------
 def test_batch_equals_standalone_runs(eng):
