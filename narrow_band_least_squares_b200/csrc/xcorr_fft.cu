@@ -326,18 +326,18 @@ __device__ __forceinline__ int pair_index(int ci, int cj, int C) { return ci * (
 // pass-1 stores of the partner butterflies f0 = t (A) and M1 - t (B); W[n] = w_L^{t n}, so B's twiddle
 // is w_L^{(M1-t) n} = e^{2 pi i n/R1} conj(W[n]); the constant factor e^{2 pi i n/R1} was applied for free
 // by feeding B's inputs to the butterfly rotated by one position (DFT shift theorem)
+// pA = sm + pad(t), pB = sm + pad(M1 - t); pad(n1 M1 + x) = pad(x) + n1 (M1 + R2): constant offsets from the two bases
 template <class S, int N1, class V>
-__device__ __forceinline__ void store_pair(const V (&zA)[S::R1], const V (&zB)[S::R1], const V (&W)[S::R1], int t,
-                                           V* sm) {
+__device__ __forceinline__ void store_pair(const V (&zA)[S::R1], const V (&zB)[S::R1], const V (&W)[S::R1], V* pA, V* pB) {
     if constexpr (N1 < S::R1) {
         if constexpr (N1 == 0) {
-            sm[S::pad(t)] = zA[0];
-            sm[S::pad(S::M1 - t)] = zB[0];
+            pA[0] = zA[0];
+            pB[0] = zB[0];
         } else {
-            sm[S::pad(N1 * S::M1 + t)] = cmul(zA[N1], W[N1]);
-            sm[S::pad(N1 * S::M1 + S::M1 - t)] = cmulc(zB[N1], W[N1]);
+            pA[N1 * (S::M1 + S::R2)] = cmul(zA[N1], W[N1]);
+            pB[N1 * (S::M1 + S::R2)] = cmulc(zB[N1], W[N1]);
         }
-        store_pair<S, N1 + 1>(zA, zB, W, t, sm);
+        store_pair<S, N1 + 1>(zA, zB, W, pA, pB);
     }
 }
 
@@ -464,15 +464,24 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         // mirror L - f is loaded: two base offsets per task, the rest are immediate offsets
         constexpr int HALF = (R1 % 2 == 0) ? R1 / 2 : (R1 + 1) / 2;
         V vi0[R1], vj0[R1], vi1[R1], vj1[R1], w1;
+        // a CTA without a second rider carries its first one twice (p1 = p0), so no rider test here.  Row bases are uniform;
+        // per task two pointers per row (direct: + t, mirrored: + L - t), every load an immediate offset from one of them
         auto load_task = [&](int t) {
-            const int md = t, mm = L - t;
+            const V *di0 = Xi0 + t, *dj0 = Xj0 + t, *dj1 = Xj1 + t, *di1 = Xi1 + t;
+            const V *mi0 = Xi0 + (L - t), *mj0 = Xj0 + (L - t), *mj1 = Xj1 + (L - t), *mi1 = Xi1 + (L - t);
 #pragma unroll
             for (int k = 0; k < R1; ++k) {
-                const int gi = k < HALF ? md + M1 * k : mm - M1 * k;
-                vi0[k] = ldg2(Xi0 + gi);
-                vj0[k] = ldg2(Xj0 + gi);
-                vj1[k] = has1 ? ldg2(Xj1 + gi) : mk2((F)0, (F)0);
-                vi1[k] = same_i ? vi0[k] : ldg2(Xi1 + gi);
+                if (k < HALF) {
+                    vi0[k] = ldg2(di0 + M1 * k);
+                    vj0[k] = ldg2(dj0 + M1 * k);
+                    vj1[k] = ldg2(dj1 + M1 * k);
+                    vi1[k] = same_i ? vi0[k] : ldg2(di1 + M1 * k);
+                } else {
+                    vi0[k] = ldg2(mi0 - M1 * k);
+                    vj0[k] = ldg2(mj0 - M1 * k);
+                    vj1[k] = ldg2(mj1 - M1 * k);
+                    vi1[k] = same_i ? vi0[k] : ldg2(mi1 - M1 * k);
+                }
             }
             w1 = ldg2(tw + t);
         };
@@ -501,7 +510,7 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             Dft<R1>::run(zA);
             Dft<R1>::run(zB);
             powers<R1>(W);
-            store_pair<S, 0>(zA, zB, W, t, sm);
+            store_pair<S, 0>(zA, zB, W, sm + S::pad(t), sm + S::pad(M1 - t));
             t = tn;
         }
     }
