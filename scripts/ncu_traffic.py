@@ -32,7 +32,7 @@ def group_of(name, state):
         if rev:      # backward pass: phase 1 then phase 3, alternating
             return "filter_bwd_phase1" if state[k] % 2 == 1 else "filter_bwd_phase3"
         return "filter_fwd_phase3" if state.get("shared_p1", True) else ("filter_fwd_phase1" if state[k] % 2 == 1 else "filter_fwd_phase3")
-    for pat, g in (("xf_spectra_kernel", "xf_spectra"), ("xf_pair_kernel", "xf_pair"), ("xf_verify_items_kernel", "xf_verify_items"),
+    for pat, g in (("xf_spectra_kernel", "xf_spectra"), ("xf_pair_kernel", "xf_pair"), ("xf_verify_items_kernel", "xf_verify_items"), ("xf_median_select_kernel", "xf_verify_items"),
                    ("xf_verify_kernel", "xf_verify"), ("xcorr_direct_kernel", "xcorr_direct"), ("stats_ols_kernel", "stats_ols"),
                    ("lts_kernel", "lts"), ("xf_audit_kernel", None)):
         if pat in name:
