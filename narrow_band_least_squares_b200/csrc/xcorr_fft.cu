@@ -643,7 +643,10 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
             g.sval[loc] = sv;
             if (g.lazy) {
                 bool approx = false;
-                if (give && cnt == 1) {
+                // one pair-window in 256 (a fixed hash of its index) is evaluated exactly although it has a single candidate:
+                // the consistency guard and the max_screen_err statistic of nbls_xcorr_stats keep watching the screen
+                const bool sampled = ((unsigned)loc * 2654435761u) >> 24 == 0u;
+                if (give && cnt == 1 && !sampled) {
                     // one lag inside the candidate band: it is the arg-max; its value is known to XF_EPS32
                     approx = true;
                     g.lag[item] = cl[0];

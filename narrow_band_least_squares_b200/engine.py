@@ -344,8 +344,9 @@ class Engine:
             yd.free()
         return np.ascontiguousarray(out)
 
-    def xcorr(self, filt, win_len, win_hop, win_count, win_first=None, max_lag=-1, method=_capi.XCORR_AUTO):
-        """filt (B, C, T) -> lag (E, P) int32, cmax (E, P)  (nbls_xcorr)."""
+    def xcorr(self, filt, win_len, win_hop, win_count, win_first=None, max_lag=-1, method=_capi.XCORR_AUTO, want_cmax=True):
+        """filt (B, C, T) -> lag (E, P) int32, cmax (E, P)  (nbls_xcorr).  ``want_cmax=False`` passes no cmax buffer (the
+        FP32-screen path then evaluates only undecided pair-windows in FP64, NBLS_OPT_LAZY_VERIFY) and returns cmax = None."""
         filt = np.asarray(filt, dtype=np.float64)
         b, c, t = filt.shape
         ld = (t + 15) // 16 * 16
@@ -364,10 +365,10 @@ class Engine:
         ld_ = DeviceArray(self, 4 * max(e, 1) * p)
         cd = DeviceArray(self, 8 * max(e, 1) * p)
         try:
-            check(self.lib.nbls_xcorr(self.ctx, C.byref(w), yd.ptr, c, ld, c * ld, ld_.ptr, cd.ptr))
+            check(self.lib.nbls_xcorr(self.ctx, C.byref(w), yd.ptr, c, ld, c * ld, ld_.ptr, cd.ptr if want_cmax else None))
             self.synchronize()
             lag = ld_.download((e, p), np.int32)
-            cmax = cd.download((e, p), np.float64)
+            cmax = cd.download((e, p), np.float64) if want_cmax else None
         finally:
             yd.free(); ld_.free(); cd.free()
         return lag, cmax

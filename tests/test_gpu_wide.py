@@ -167,6 +167,10 @@ def test_fp32_screen_adversarial_equals_time_domain(eng, kind, method):
         neq = int((lag != ref_lag).sum())
         assert neq == 0, f"{kind} N={n}: {neq} of {lag.size} integer lags differ from the time-domain kernel"
         assert np.allclose(cmax, ref_cmax, rtol=0, atol=1e-11, equal_nan=True), (kind, n)
+        # the lazy path (no cmax buffer: only undecided pair-windows are evaluated in FP64) must return the same lags
+        lag_lazy, _ = eng.xcorr(filt, [n], [hop], [nwin], method=method, want_cmax=False)
+        neq = int((lag_lazy != ref_lag).sum())
+        assert neq == 0, f"{kind} N={n}: {neq} of {lag.size} lazy-path lags differ from the time-domain kernel"
         total_pw += lag.size
     assert total_pw >= 100000
     assert worst < 1e-5, f"{kind}: FP32 screen error over all lags {worst:.3g} reaches half the candidate band"
