@@ -28,6 +28,7 @@
 // appended to a list and re-evaluated by the time-domain FP64 kernel (xcorr_direct.cu, list mode),
 // whose first-maximum-wins semantics match np.argmax.  For every other pair-window the FFT arg-max
 // provably equals the time-domain one.
+#include <cuda_pipeline.h>
 #include <float.h>
 #include <limits.h>
 #include <math.h>
@@ -568,6 +569,24 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         }
         if (lane == 0) { smax[0][warp] = mr; smax[1][warp] = mi; }
         if (tid < 2) scnt[tid] = 0;
+        // the two threads that finish the CTA need their rider's energies (and the stage-A partial energies): asynchronous
+        // 8-byte copies into shared memory start here, fly under the two barriers and cost no registers, instead of a
+        // chain of dependent global loads holding the CTA's 68 KB of shared memory at the very end
+        __shared__ double s_en[2][6];
+        if (tid < 2) {
+            const int wl_ = tid == 0 ? wl0 : wl1, ci_ = tid == 0 ? i0 : i1, cj_ = tid == 0 ? j0 : j1;
+            __pipeline_memcpy_async(&s_en[tid][0], g.energy + (int64_t)wl_ * g.C + ci_, 8);
+            __pipeline_memcpy_async(&s_en[tid][1], g.energy + (int64_t)wl_ * g.C + cj_, 8);
+            if (g.lazy && g.k0 >= 0) {
+                const double* pi = g.part + ((int64_t)wl_ * g.C + ci_) * 2;
+                const double* pj = g.part + ((int64_t)wl_ * g.C + cj_) * 2;
+                __pipeline_memcpy_async(&s_en[tid][2], pi, 8);
+                __pipeline_memcpy_async(&s_en[tid][3], pi + 1, 8);
+                __pipeline_memcpy_async(&s_en[tid][4], pj, 8);
+                __pipeline_memcpy_async(&s_en[tid][5], pj + 1, 8);
+            }
+            __pipeline_commit();
+        }
         __syncthreads();
         const float lmr = mr, lmi = mi;       // warp-level maxima
         mr = smax[0][0]; mi = smax[1][0];
@@ -608,8 +627,8 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
         if (tid < 2 && (tid == 0 || has1)) {
             const int p = tid == 0 ? p0 : p1, wl = tid == 0 ? wl0 : wl1;
             const int ci = tid == 0 ? i0 : i1, cj = tid == 0 ? j0 : j1;
-            const double Ei = g.energy[(int64_t)wl * g.C + ci], Ej = g.energy[(int64_t)wl * g.C + cj];
-            const double den = sqrt(Ei * Ej);
+            __pipeline_wait_prior(0);
+            const double den = sqrt(s_en[tid][0] * s_en[tid][1]);
             const int64_t item = (int64_t)(g.w0 + wl) * g.P + p;
             const int64_t loc = (int64_t)wl * g.P + p;
             const int cnt = scnt[tid];
@@ -653,9 +672,7 @@ __global__ void __launch_bounds__(T, MINB) xf_pair_kernel(XfArgs g) {
                     if (g.cmax) g.cmax[item] = (double)sv;
                     if (g.k0 >= 0) {
                         // stage-A proof (see xf_verify_kernel) on the screen value less its error, in normalised units
-                        const double* pi = g.part + ((int64_t)wl * g.C + ci) * 2;
-                        const double* pj = g.part + ((int64_t)wl * g.C + cj) * 2;
-                        const double b2 = fmax(pi[1] * pj[0], pi[0] * pj[1]);
+                        const double b2 = fmax(s_en[tid][3] * s_en[tid][4], s_en[tid][2] * s_en[tid][5]);
                         if (!(((double)sv - XF_EPS32) * den > sqrt(b2) * (1.0 + 1e-12))) g.pf_flag[loc] = 1;
                     }
                 } else if (give) {
