@@ -96,7 +96,6 @@ struct nbls_ctx {
     nbls::DevBuf wfail;                     // two-stage lag search: failing pair-window items and the window list of stage B
     nbls::DevBuf lazy;                      // NBLS_OPT_LAZY_VERIFY: approximate-cmax flags and the list of pair-windows to evaluate
     bool cmax_median_only = false;          // set by nbls_run_* when the caller wants no per-pair cmax
-    int64_t lazy_exact = 0, lazy_skipped = 0;
     int ts_skip = 0;                        // bands left to the single-stage search after a band that mostly failed
     int64_t ts_windows = 0, ts_redone = 0;  // two-stage statistics: windows searched / redone over all lags
     std::map<int, void*> fft_tw;            // twiddle tables by transform length (device)

@@ -29,6 +29,18 @@ def test_capi_exports_every_declared_symbol():
     assert lib.nbls_version() >= 100
 
 
+def test_capi_option_numbers_match_the_header():
+    """NBLS_OPT_* of include/nbls.h and _capi.OPT_* (what Engine.set_option and bench.py --opt use) are the same numbers,
+    every one below NBLS_OPT_COUNT; NBLS_XCORR_STATIC_MAX_ENTRIES is stated in the header."""
+    hdr = open(os.path.join(ROOT, "include", "nbls.h")).read()
+    defs = {k: int(v) for k, v in re.findall(r"#define\s+NBLS_OPT_([A-Z0-9_]+)\s+(\d+)", hdr)}
+    count = defs.pop("COUNT")
+    assert len(defs) >= 11 and sorted(defs.values()) == list(range(len(defs))) and max(defs.values()) < count
+    for name, value in defs.items():
+        assert getattr(_capi, "OPT_" + name) == value, name
+    assert re.search(r"#define\s+NBLS_XCORR_STATIC_MAX_ENTRIES\s+262144", hdr)
+
+
 def test_no_cuda_device_fails_loudly():
     import ctypes as C
     lib = _capi.load()
