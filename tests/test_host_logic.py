@@ -409,3 +409,38 @@ def test_deal_arrays_by_array_then_segment():
     items = deal_arrays(3, 8)                     # 8 ranks, 3 arrays: groups of 3, 3 and 2 ranks share an array by segment
     assert [it[0] for it in items] == [(0, 0, 3), (0, 1, 3), (0, 2, 3), (1, 0, 3), (1, 1, 3), (1, 2, 3), (2, 0, 2), (2, 1, 2)]
     assert deal_arrays(5, 1) == [[(a, 0, 1) for a in range(5)]]
+
+
+def test_lazy_verification_median_rule():
+    """The rule of xf_median_select_kernel (csrc/xcorr_fft.cu), restated in numpy: stored values v within eps of the exact
+    ones e; after the approximate entries within 2 eps of either middle order statistic of v are replaced by their exact
+    values, np.nanmedian of the stored array equals np.nanmedian(e) - whatever the errors were (worst cases included:
+    values clustered inside the band, errors at +-eps, NaNs, entries that are exact already)."""
+    rng = np.random.default_rng(5)
+    eps = 1e-5
+    for trial in range(4000):
+        p = int(rng.choice([6, 15, 66, 299, 300]))
+        kind = trial % 4
+        if kind == 0:
+            e = rng.uniform(0.0, 1.0, p)
+        elif kind == 1:                               # everything inside a few bands of the median
+            e = 0.7 + rng.uniform(-4 * eps, 4 * eps, p)
+        elif kind == 2:                               # ties and near-ties
+            e = np.round(rng.uniform(0.5, 0.5 + 20 * eps, p) / (eps / 2)) * (eps / 2)
+        else:
+            e = np.concatenate([rng.uniform(0, 1, p // 2), 0.5 + rng.uniform(-2 * eps, 2 * eps, p - p // 2)])
+        err = rng.choice([-eps, eps, 0.0], p) if trial % 3 == 0 else rng.uniform(-eps, eps, p)
+        apx = rng.random(p) < 0.9                     # some entries are exact already (multi-candidate pairs)
+        e[rng.random(p) < (0.05 if trial % 5 == 0 else 0.0)] = np.nan      # dead pairs
+        v = np.where(apx, e + err, e)
+        ok = ~np.isnan(v)
+        m = int(ok.sum())
+        if m == 0:
+            continue
+        srt = np.sort(v[ok])
+        hi = srt[m // 2]
+        lo = hi if m % 2 else srt[m // 2 - 1]
+        band = 2.0 * eps * (1.0 + 1e-9)
+        need = apx & ok & ((np.abs(v - lo) <= band) | (np.abs(v - hi) <= band))
+        v2 = np.where(need, e, v)
+        assert np.nanmedian(v2) == np.nanmedian(e), (trial, p, kind)
