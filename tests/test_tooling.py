@@ -106,3 +106,26 @@ def test_staged_reference_archive_runs_the_reference_driver():
         "print('ok')\n" % ROOT)
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True)
     assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]
+
+
+def test_committed_headline_line_keeps_the_bench_contract():
+    """The last headline bench line (profiles/r2_bench_c3_final4.json, unedited stdout of bench.py) carries every key the
+    bench contract names, with the metric and workload of BASELINE.json."""
+    d = json.loads(open(os.path.join(ROOT, "profiles", "r2_bench_c3_final4.json")).read())
+    base = json.load(open(os.path.join(ROOT, "BASELINE.json")))
+    for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+              "vs_baseline", "dtype", "data", "config", "roofline", "cpu_baseline", "e2e", "gpu_launches", "clocks", "parity"):
+        assert k in d, k
+    assert d["n_gpus"] == 1 and d["warmup"] >= 3 and d["higher_is_better"] is True and d["gpu_launches"] > 0
+    assert d["unit"] == base.get("unit", d["unit"]) and "workload" in d["config"] and d["config"]["workload"].startswith("c3")
+    r = d["roofline"]
+    assert {"bound", "achieved", "peak", "unit", "frac", "traffic"} <= set(r) and abs(r["frac"] - r["achieved"] / r["peak"]) < 1e-9
+    c = d["cpu_baseline"]
+    assert {"value", "unit", "cores", "kind", "sample"} <= set(c) and c["kind"] == "reference" and c["cores"] >= 1
+    e = d["e2e"]
+    assert e["h2d_bytes_per_step"] > 0 and e["d2h_bytes_per_step"] > 0 and 0 < e["value"] <= 1.05 * d["value"]
+    assert abs(d["value"] - d["config"]["estimates_per_step"] / (d["ms_per_step"] * 1e-3)) / d["value"] < 1e-6
+    assert not ({"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"} & set(d["clocks"]["reasons"]))
+    p = d["parity"]
+    assert p["vs_oracle"]["lag_mismatches"] == 0 and p["timed_path_vs_cmax_path"]["lag_mismatches"] == 0
+    assert p["timed_path_vs_cmax_path"]["estimates_bit_identical"] and p["timed_path_vs_cmax_path"]["max_abs_dmdccm"] <= 1e-15
